@@ -1,0 +1,531 @@
+// Host (CPU) transport — SURVEY W9.
+//
+// The reference runs CPU nodes over libipc TCP sockets (examples/mnist.sh: four CPU processes).
+// Here same-host CPU ranks share one POSIX shared-memory segment that holds every rank's
+// "symmetric heap", and run the SAME algorithms as the GPU kernels (owner-computes two-shot
+// reduce + push, double-buffered elastic averaging, slice-relay broadcast, center-resident async
+// EASGD) with C++11 atomics as the release/acquire flag protocol.  It backs BASELINE config #1
+// (2 CPU processes, MNIST AllReduceSGD) and lets the multi-rank logic be tested without a GPU.
+//
+// Layout of the segment:  [header 4 KiB][heap of rank 0][heap of rank 1]...   and every heap
+// starts with a HostPad (DL_PAD_BYTES reserved, as on the GPU).
+#include <atomic>
+#include <cerrno>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <fcntl.h>
+#include <sched.h>
+#include <sys/mman.h>
+#include <sys/stat.h>
+#include <time.h>
+#include <unistd.h>
+
+#include "../include/distlearn_b200.h"
+
+namespace {
+
+thread_local char g_err[512] = "";
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+constexpr uint64_t kMagic = 0x444c42323030484full;  // "DLB200HO"
+constexpr size_t kHeaderBytes = 4096;
+
+struct Header {
+  std::atomic<uint64_t> magic;
+  uint32_t world;
+  uint32_t reserved;
+  uint64_t heap_bytes;
+  std::atomic<uint32_t> attached;
+};
+
+struct HostPad {
+  std::atomic<uint64_t> flags[DL_NUM_CHANNELS][2][DL_MAX_RANKS];
+  uint64_t aux[DL_NUM_CHANNELS][2][DL_MAX_RANKS];  // published before the flag (release), read after (acquire)
+  uint32_t epoch[DL_NUM_CHANNELS];
+  // async EASGD control (server side)
+  std::atomic<uint32_t> ticket_next;
+  std::atomic<uint32_t> ticket_serving;
+  std::atomic<uint64_t> sync_count;
+  std::atomic<uint64_t> mailbox[16];
+};
+static_assert(sizeof(HostPad) <= DL_PAD_BYTES, "host pad too large");
+
+struct Handle {
+  int rank, world;
+  size_t heap_bytes, total_bytes;
+  char* map;
+  char name[128];
+  double timeout_s;
+  char* heap(int r) const { return map + kHeaderBytes + static_cast<size_t>(r) * heap_bytes; }
+  HostPad* pad(int r) const { return reinterpret_cast<HostPad*>(heap(r)); }
+  template <typename T>
+  T* at(int r, uint64_t off) const {
+    return reinterpret_cast<T*>(heap(r) + off);
+  }
+};
+
+double now_s() {
+  struct timespec ts;
+  clock_gettime(CLOCK_MONOTONIC, &ts);
+  return ts.tv_sec + ts.tv_nsec * 1e-9;
+}
+
+// bounded spin with back-off: yields quickly because CI machines have fewer cores than ranks
+struct Spinner {
+  unsigned polls = 0;
+  double t0 = 0.0;
+  double limit;
+  explicit Spinner(double l) : limit(l) {}
+  bool wait_more() {
+    ++polls;
+    if (polls < 64) return true;
+    if (polls < 4096) {
+      sched_yield();
+    } else {
+      struct timespec ts = {0, 50000};
+      nanosleep(&ts, nullptr);
+    }
+    if ((polls & 255u) == 0) {
+      const double t = now_s();
+      if (t0 == 0.0) t0 = t;
+      if (t - t0 > limit) return false;
+    }
+    return true;
+  }
+};
+
+// Cross-rank barrier; returns 0 or DL_ETIMEOUT.  pay_out[r] receives rank r's payload word.
+int barrier(Handle* h, int ch, uint32_t payload, uint32_t* pay_out, uint64_t aux = 0, uint64_t* aux_out = nullptr) {
+  HostPad* mine = h->pad(h->rank);
+  const uint32_t e = mine->epoch[ch] + 1u;
+  const uint64_t word = (static_cast<uint64_t>(e) << 32) | payload;
+  for (int r = 0; r < h->world; ++r) {
+    h->pad(r)->aux[ch][e & 1u][h->rank] = aux;
+    h->pad(r)->flags[ch][e & 1u][h->rank].store(word, std::memory_order_release);
+  }
+  for (int r = 0; r < h->world; ++r) {
+    Spinner sp(h->timeout_s);
+    uint64_t w;
+    while (static_cast<uint32_t>((w = mine->flags[ch][e & 1u][r].load(std::memory_order_acquire)) >> 32) != e) {
+      if (!sp.wait_more()) {
+        set_error("rank %d timed out waiting for rank %d (channel %d, epoch %u)", h->rank, r, ch, e);
+        mine->epoch[ch] = e;
+        return DL_ETIMEOUT;
+      }
+    }
+    if (pay_out) pay_out[r] = static_cast<uint32_t>(w);
+    if (aux_out) aux_out[r] = mine->aux[ch][e & 1u][r];
+  }
+  mine->epoch[ch] = e;
+  return DL_OK;
+}
+
+uint32_t decode(const Handle* h, const uint32_t* pay, dl_result_t* res, int* n_active) {
+  uint32_t mask = 0;
+  int n = 0;
+  for (int r = 0; r < h->world; ++r) {
+    if (pay[r] & 3u) mask |= 1u << r;  // data included
+    if (pay[r] & 1u) ++n;              // counted as a contributor
+  }
+  if (res) {
+    memset(res, 0, sizeof(*res));
+    for (int r = 0; r < h->world; ++r) res->payload[r] = pay[r] >> 2;
+    res->n_active = static_cast<uint32_t>(n);
+  }
+  *n_active = n;
+  return mask;
+}
+
+struct Slice {
+  uint64_t len, begin, end;
+};
+Slice slice_of(uint64_t n, int rank, int world) {
+  Slice s;
+  s.len = (n + world - 1) / world;
+  s.begin = s.len * rank;
+  s.end = s.begin + s.len;
+  if (s.begin > n) s.begin = n;
+  if (s.end > n) s.end = n;
+  return s;
+}
+
+int check(Handle* h, int ch) {
+  if (!h) {
+    set_error("null handle");
+    return DL_EINVAL;
+  }
+  if (ch < 0 || ch >= DL_NUM_CHANNELS) {
+    set_error("bad channel %d", ch);
+    return DL_EINVAL;
+  }
+  return DL_OK;
+}
+
+template <typename T>
+void reduce_typed(Handle* h, uint64_t off, uint64_t n, uint32_t mask, bool scale, int n_act) {
+  // owner-computes over this rank's slice, push to everyone (same as the two-shot GPU kernel)
+  const Slice s = slice_of(n, h->rank, h->world);
+  const T* src[DL_MAX_RANKS];
+  T* dst[DL_MAX_RANKS];
+  for (int r = 0; r < h->world; ++r) {
+    src[r] = h->at<T>(r, off);
+    dst[r] = h->at<T>(r, off);
+  }
+  for (uint64_t i = s.begin; i < s.end; ++i) {
+    T acc = (mask & 1u) ? src[0][i] : T(0);
+    for (int r = 1; r < h->world; ++r) acc += ((mask >> r) & 1u) ? src[r][i] : T(0);
+    if (scale && n_act > 1) acc = static_cast<T>(acc * (T(1) / static_cast<T>(n_act)));
+    for (int r = 0; r < h->world; ++r) dst[r][i] = acc;
+  }
+}
+template <>
+void reduce_typed<float>(Handle* h, uint64_t off, uint64_t n, uint32_t mask, bool scale, int n_act) {
+  const Slice s = slice_of(n, h->rank, h->world);
+  const float inv = (scale && n_act > 1) ? 1.f / static_cast<float>(n_act) : 1.f;
+  for (uint64_t i = s.begin; i < s.end; ++i) {
+    float acc = (mask & 1u) ? h->at<float>(0, off)[i] : 0.f;
+    for (int r = 1; r < h->world; ++r) acc += ((mask >> r) & 1u) ? h->at<float>(r, off)[i] : 0.f;
+    acc *= inv;
+    for (int r = 0; r < h->world; ++r) h->at<float>(r, off)[i] = acc;
+  }
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* dlh_last_error(void) { return g_err; }
+
+int dlh_open(const char* name, int rank, int world, uint64_t heap_bytes, double timeout_s, void** out) {
+  if (world < 1 || world > DL_MAX_RANKS || rank < 0 || rank >= world || heap_bytes < DL_PAD_BYTES || heap_bytes % 4096) {
+    set_error("dlh_open: bad arguments (rank %d world %d heap %llu)", rank, world, (unsigned long long)heap_bytes);
+    return DL_EINVAL;
+  }
+  const size_t total = kHeaderBytes + static_cast<size_t>(world) * heap_bytes;
+  const double limit = timeout_s > 0 ? timeout_s : 60.0;
+  int fd = -1;
+  if (rank == 0) {
+    shm_unlink(name);
+    fd = shm_open(name, O_CREAT | O_EXCL | O_RDWR, 0600);
+    if (fd < 0 || ftruncate(fd, static_cast<off_t>(total)) != 0) {
+      set_error("shm_open/ftruncate '%s': %s", name, strerror(errno));
+      if (fd >= 0) close(fd);
+      return DL_ESYS;
+    }
+  } else {
+    const double t0 = now_s();
+    while (true) {
+      fd = shm_open(name, O_RDWR, 0600);
+      if (fd >= 0) {
+        struct stat st;
+        if (fstat(fd, &st) == 0 && static_cast<size_t>(st.st_size) >= total) break;
+        close(fd);
+        fd = -1;
+      }
+      if (now_s() - t0 > limit) {
+        set_error("timed out waiting for rank 0 to create '%s'", name);
+        return DL_ETIMEOUT;
+      }
+      usleep(1000);
+    }
+  }
+  void* map = mmap(nullptr, total, PROT_READ | PROT_WRITE, MAP_SHARED, fd, 0);
+  close(fd);
+  if (map == MAP_FAILED) {
+    set_error("mmap '%s': %s", name, strerror(errno));
+    return DL_ESYS;
+  }
+  Handle* h = new Handle();
+  h->rank = rank;
+  h->world = world;
+  h->heap_bytes = heap_bytes;
+  h->total_bytes = total;
+  h->map = static_cast<char*>(map);
+  h->timeout_s = limit;
+  snprintf(h->name, sizeof(h->name), "%s", name);
+  Header* hdr = reinterpret_cast<Header*>(h->map);
+  if (rank == 0) {
+    // a fresh segment is zero-filled by the kernel: pads start at epoch 0
+    hdr->world = static_cast<uint32_t>(world);
+    hdr->heap_bytes = heap_bytes;
+    hdr->attached.store(1, std::memory_order_relaxed);
+    hdr->magic.store(kMagic, std::memory_order_release);
+  } else {
+    const double t0 = now_s();
+    while (hdr->magic.load(std::memory_order_acquire) != kMagic) {
+      if (now_s() - t0 > limit) {
+        set_error("timed out waiting for rank 0 to initialise '%s'", name);
+        munmap(map, total);
+        delete h;
+        return DL_ETIMEOUT;
+      }
+      usleep(500);
+    }
+    if (hdr->world != static_cast<uint32_t>(world) || hdr->heap_bytes != heap_bytes) {
+      set_error("segment '%s' was created with a different geometry", name);
+      munmap(map, total);
+      delete h;
+      return DL_EINVAL;
+    }
+    hdr->attached.fetch_add(1, std::memory_order_acq_rel);
+  }
+  // everybody waits until all ranks are attached, then rank 0 may unlink the name
+  {
+    const double t0 = now_s();
+    while (hdr->attached.load(std::memory_order_acquire) < static_cast<uint32_t>(world)) {
+      if (now_s() - t0 > limit) {
+        set_error("timed out waiting for all %d ranks to attach to '%s'", world, name);
+        munmap(map, total);
+        delete h;
+        return DL_ETIMEOUT;
+      }
+      usleep(500);
+    }
+  }
+  *out = h;
+  return DL_OK;
+}
+
+int dlh_close(void* handle, int unlink_name) {
+  Handle* h = static_cast<Handle*>(handle);
+  if (!h) return DL_OK;
+  if (unlink_name) shm_unlink(h->name);
+  munmap(h->map, h->total_bytes);
+  delete h;
+  return DL_OK;
+}
+
+void* dlh_base(void* handle, int rank) {
+  Handle* h = static_cast<Handle*>(handle);
+  if (!h || rank < 0 || rank >= h->world) return nullptr;
+  return h->heap(rank);
+}
+
+int dlh_set_timeout(void* handle, double seconds) {
+  Handle* h = static_cast<Handle*>(handle);
+  if (!h) return DL_EINVAL;
+  h->timeout_s = seconds;
+  return DL_OK;
+}
+
+int dlh_barrier(void* handle, int active, uint32_t payload, int channel, dl_result_t* res) {
+  Handle* h = static_cast<Handle*>(handle);
+  int rc = check(h, channel);
+  if (rc) return rc;
+  uint32_t pay[DL_MAX_RANKS] = {0};
+  rc = barrier(h, channel, (payload << 2) | (static_cast<uint32_t>(active) & 3u), pay);
+  if (rc) return rc;
+  int n;
+  decode(h, pay, res, &n);
+  return DL_OK;
+}
+
+int dlh_allreduce(void* handle, int dtype, uint64_t off, uint64_t n, int active, uint32_t payload, int scale,
+                  int channel, dl_result_t* res) {
+  Handle* h = static_cast<Handle*>(handle);
+  int rc = check(h, channel);
+  if (rc) return rc;
+  uint32_t pay[DL_MAX_RANKS] = {0};
+  uint64_t auxs[DL_MAX_RANKS] = {0};
+  rc = barrier(h, channel, (payload << 2) | (static_cast<uint32_t>(active) & 3u), pay, scale ? 1u : 0u, auxs);
+  if (rc) return rc;
+  int n_act;
+  const uint32_t mask = decode(h, pay, res, &n_act);
+  if (mask) scale = static_cast<int>(auxs[__builtin_ctz(mask)] & 1u);  // the lowest active rank dictates
+  switch (dtype) {
+    case DL_F32: reduce_typed<float>(h, off, n, mask, scale != 0, n_act); break;
+    case DL_I32: reduce_typed<int32_t>(h, off, n, mask, false, n_act); break;
+    case DL_I64: reduce_typed<int64_t>(h, off, n, mask, false, n_act); break;
+    case DL_F64: reduce_typed<double>(h, off, n, mask, scale != 0, n_act); break;
+    default: set_error("bad dtype %d", dtype); return DL_EINVAL;
+  }
+  return barrier(h, channel, 0u, nullptr);
+}
+
+int dlh_fused_sgd(void* handle, uint64_t g_off, uint64_t p_off, uint64_t m_off, uint64_t n, float lr, float momentum,
+                  float wd, int nesterov, int active, uint32_t payload, int zero_grads, int channel, dl_result_t* res) {
+  Handle* h = static_cast<Handle*>(handle);
+  int rc = check(h, channel);
+  if (rc) return rc;
+  uint32_t pay[DL_MAX_RANKS] = {0};
+  uint64_t auxs[DL_MAX_RANKS] = {0};
+  uint32_t lr_bits;
+  memcpy(&lr_bits, &lr, 4);
+  rc = barrier(h, channel, (payload << 2) | (static_cast<uint32_t>(active) & 3u), pay, lr_bits, auxs);
+  if (rc) return rc;
+  int n_act;
+  const uint32_t mask = decode(h, pay, res, &n_act);
+  if (mask) {  // the learning rate of the lowest active rank wins (draining ranks just follow)
+    lr_bits = static_cast<uint32_t>(auxs[__builtin_ctz(mask)]);
+    memcpy(&lr, &lr_bits, 4);
+  }
+  if (n_act > 0) {
+    const Slice s = slice_of(n, h->rank, h->world);
+    const float inv = n_act > 1 ? 1.f / static_cast<float>(n_act) : 1.f;
+    float* p_loc = h->at<float>(h->rank, p_off);
+    float* m_loc = m_off ? h->at<float>(h->rank, m_off) : nullptr;
+    for (uint64_t i = s.begin; i < s.end; ++i) {
+      float acc = (mask & 1u) ? h->at<float>(0, g_off)[i] : 0.f;
+      for (int r = 1; r < h->world; ++r) acc += ((mask >> r) & 1u) ? h->at<float>(r, g_off)[i] : 0.f;
+      float g = acc * inv;
+      float p = p_loc[i];
+      if (wd != 0.f) g += wd * p;
+      if (m_loc) {
+        const float m = momentum * m_loc[i] + g;
+        m_loc[i] = m;
+        g = nesterov ? g + momentum * m : m;
+      }
+      p -= lr * g;
+      for (int r = 0; r < h->world; ++r) h->at<float>(r, p_off)[i] = p;
+    }
+  }
+  rc = barrier(h, channel, 0u, nullptr);
+  if (rc) return rc;
+  if (zero_grads) memset(h->at<float>(h->rank, g_off), 0, n * sizeof(float));
+  return DL_OK;
+}
+
+int dlh_fused_ea(void* handle, uint64_t x_off, uint64_t c_off, uint64_t cnew_off, uint64_t n, float alpha, int active,
+                 uint32_t payload, int channel, dl_result_t* res) {
+  Handle* h = static_cast<Handle*>(handle);
+  int rc = check(h, channel);
+  if (rc) return rc;
+  if (c_off == cnew_off) {
+    set_error("dlh_fused_ea: next-center buffer must differ from the current one");
+    return DL_EINVAL;
+  }
+  uint32_t pay[DL_MAX_RANKS] = {0};
+  rc = barrier(h, channel, (payload << 2) | (static_cast<uint32_t>(active) & 3u), pay);
+  if (rc) return rc;
+  int n_act;
+  decode(h, pay, res, &n_act);
+  const float* c_old = h->at<float>(h->rank, c_off);
+  if (n_act > 0) {
+    const Slice s = slice_of(n, h->rank, h->world);
+    for (uint64_t i = s.begin; i < s.end; ++i) {
+      const float cv = c_old[i];
+      float sum = 0.f;
+      for (int r = 0; r < h->world; ++r) sum += (h->at<float>(r, x_off)[i] - cv) * alpha;
+      const float cn = cv + sum;
+      for (int r = 0; r < h->world; ++r) h->at<float>(r, cnew_off)[i] = cn;
+    }
+  }
+  rc = barrier(h, channel, 0u, nullptr);
+  if (rc) return rc;
+  if (n_act > 0) {
+    float* x = h->at<float>(h->rank, x_off);
+    for (uint64_t i = 0; i < n; ++i) x[i] -= (x[i] - c_old[i]) * alpha;
+  } else {
+    memcpy(h->at<float>(h->rank, cnew_off), c_old, n * sizeof(float));
+  }
+  return DL_OK;
+}
+
+int dlh_broadcast(void* handle, uint64_t off, uint64_t off2, uint64_t n, int root, uint32_t payload, int channel,
+                  dl_result_t* res) {
+  Handle* h = static_cast<Handle*>(handle);
+  int rc = check(h, channel);
+  if (rc) return rc;
+  if (root < 0 || root >= h->world) {
+    set_error("bad root %d", root);
+    return DL_EINVAL;
+  }
+  uint32_t pay[DL_MAX_RANKS] = {0};
+  rc = barrier(h, channel, (payload << 2) | 1u, pay);
+  if (rc) return rc;
+  int n_act;
+  decode(h, pay, res, &n_act);
+  const Slice s = slice_of(n, h->rank, h->world);
+  const float* src = h->at<float>(root, off);
+  for (int r = 0; r < h->world; ++r) {
+    if (r != root) memcpy(h->at<float>(r, off) + s.begin, src + s.begin, (s.end - s.begin) * sizeof(float));
+    if (off2) memcpy(h->at<float>(r, off2) + s.begin, src + s.begin, (s.end - s.begin) * sizeof(float));
+  }
+  return barrier(h, channel, 0u, nullptr);
+}
+
+// Async EASGD client sync against a center resident in `server`'s heap (lua/AsyncEA.lua:134-146).
+int dlh_async_ea_client(void* handle, int server, float* x, uint64_t c_off, uint64_t n, float alpha, int exclusive) {
+  Handle* h = static_cast<Handle*>(handle);
+  if (!h || server < 0 || server >= h->world) {
+    set_error("bad server rank");
+    return DL_EINVAL;
+  }
+  HostPad* srv = h->pad(server);
+  uint32_t ticket = 0;
+  if (exclusive) {
+    ticket = srv->ticket_next.fetch_add(1, std::memory_order_relaxed);
+    Spinner sp(h->timeout_s);
+    while (srv->ticket_serving.load(std::memory_order_acquire) != ticket) {
+      if (!sp.wait_more()) {
+        set_error("timed out waiting for the center lock (ticket %u)", ticket);
+        return DL_ETIMEOUT;
+      }
+    }
+  }
+  float* center = h->at<float>(server, c_off);
+  if (exclusive) {
+    for (uint64_t i = 0; i < n; ++i) {
+      const float d = (x[i] - center[i]) * alpha;
+      x[i] -= d;
+      center[i] += d;
+    }
+    srv->ticket_serving.store(ticket + 1u, std::memory_order_release);
+  } else {
+    for (uint64_t i = 0; i < n; ++i) {
+      std::atomic<uint32_t>* cell = reinterpret_cast<std::atomic<uint32_t>*>(center + i);
+      uint32_t old_bits = cell->load(std::memory_order_relaxed);
+      float cv;
+      memcpy(&cv, &old_bits, 4);
+      const float d = (x[i] - cv) * alpha;
+      x[i] -= d;
+      // atomic float add (CAS loop), the CPU counterpart of red.global.add.f32
+      while (true) {
+        float cur;
+        memcpy(&cur, &old_bits, 4);
+        const float nv = cur + d;
+        uint32_t new_bits;
+        memcpy(&new_bits, &nv, 4);
+        if (cell->compare_exchange_weak(old_bits, new_bits, std::memory_order_relaxed)) break;
+      }
+    }
+  }
+  srv->sync_count.fetch_add(1, std::memory_order_release);
+  return DL_OK;
+}
+
+int dlh_async_sync_count(void* handle, int server, uint64_t* count) {
+  Handle* h = static_cast<Handle*>(handle);
+  if (!h || server < 0 || server >= h->world || !count) return DL_EINVAL;
+  *count = h->pad(server)->sync_count.load(std::memory_order_acquire);
+  return DL_OK;
+}
+
+int dlh_mailbox_write(void* handle, int rank, int index, uint64_t value) {
+  Handle* h = static_cast<Handle*>(handle);
+  if (!h || rank < 0 || rank >= h->world || index < 0 || index >= 16) return DL_EINVAL;
+  h->pad(rank)->mailbox[index].store(value, std::memory_order_release);
+  return DL_OK;
+}
+
+int dlh_mailbox_read(void* handle, int rank, int index, uint64_t* value) {
+  Handle* h = static_cast<Handle*>(handle);
+  if (!h || rank < 0 || rank >= h->world || index < 0 || index >= 16 || !value) return DL_EINVAL;
+  *value = h->pad(rank)->mailbox[index].load(std::memory_order_acquire);
+  return DL_OK;
+}
+
+int dlh_peer_pull(void* handle, int src_rank, uint64_t off, float* dst, uint64_t n) {
+  Handle* h = static_cast<Handle*>(handle);
+  if (!h || src_rank < 0 || src_rank >= h->world) return DL_EINVAL;
+  memcpy(dst, h->at<float>(src_rank, off), n * sizeof(float));
+  return DL_OK;
+}
+
+}  // extern "C"

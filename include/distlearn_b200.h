@@ -1,0 +1,180 @@
+/*
+ * distlearn_b200 — C ABI of the native library (libdistlearn_b200.so).
+ *
+ * Everything the Python package does on a GPU goes through these entry points
+ * (ctypes), so a C/C++ trainer can use them too.  All functions return 0 on
+ * success and a negative DL_E* code on failure; dl_last_error() gives the text.
+ *
+ * Reference parity is cited as path:line into shanlior/torch-distlearn.
+ */
+#ifndef DISTLEARN_B200_H
+#define DISTLEARN_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DL_MAX_RANKS 8      /* one NVSwitch domain (HGX B200) */
+#define DL_MAX_BLOCKS 160   /* >= 148 SMs: one persistent CTA per SM */
+#define DL_NUM_CHANNELS 4   /* independent signal pads (one per concurrent stream) */
+#define DL_PAD_BYTES (256u * 1024u) /* bytes reserved at the start of every heap for signalling */
+
+#define DL_OK 0
+#define DL_EINVAL (-1)
+#define DL_ECUDA (-2)
+#define DL_EUNSUPPORTED (-3)
+#define DL_ESYS (-4)
+#define DL_ETIMEOUT (-5)
+
+/* collective algorithm variants (chosen per message size by the variant table) */
+#define DL_VARIANT_ONESHOT 0 /* every rank reads all peers, reduces in rank order          */
+#define DL_VARIANT_TWOSHOT 1 /* owner-computes reduce-scatter + push all-gather over P2P   */
+#define DL_VARIANT_NVLS 2    /* multimem.ld_reduce + multimem.st through the NVSwitch      */
+
+/* data types of the plain all-reduce */
+#define DL_F32 0
+#define DL_I32 1
+#define DL_I64 2
+#define DL_F64 3
+
+/*
+ * A communicator as the kernels see it: the same heap mapped from every rank.
+ * base[r] is rank r's heap as addressable from THIS process (base[rank] is the
+ * local allocation); mc is the multicast (NVLS) mapping of the same heap or
+ * NULL.  The first DL_PAD_BYTES of every heap are the signal pad.
+ * With emulate != 0 all `world` heaps live on one GPU and one cooperative
+ * launch plays every rank (gridDim.y = world) — the single-GPU test mode.
+ */
+typedef struct dl_comm {
+  int32_t rank;
+  int32_t world;
+  int32_t emulate;
+  int32_t reserved;
+  void* base[DL_MAX_RANKS];
+  void* mc;
+  uint64_t timeout_ns; /* bounded spin: 0 = default 20 s */
+} dl_comm_t;
+
+/* Per-call result words the kernels leave in the local signal pad. */
+typedef struct dl_result {
+  uint32_t payload[DL_MAX_RANKS]; /* what each rank published at the arrival barrier */
+  uint32_t n_active;              /* number of ranks that contributed               */
+  uint32_t error;                 /* 0, or DL_ETIMEOUT (positive) if a spin gave up */
+} dl_result_t;
+
+const char* dl_last_error(void);
+int dl_version(void);
+
+/* ---- symmetric heap: CUDA VMM + POSIX-fd export (+ multicast), cudaIpc fallback ---- */
+/* Replaces libipc's socket transport + CUDA-IPC hint (examples/mnist.lua:93). */
+int dl_device_caps(int dev, int* vmm, int* fd_handles, int* multicast);
+int dl_vmm_granularity(int dev, size_t* gran);
+int dl_vmm_alloc(int dev, size_t bytes, uint64_t* handle, int* fd);
+int dl_vmm_import(int fd, uint64_t* handle);
+int dl_vmm_map(int dev, uint64_t handle, size_t bytes, void** ptr);
+int dl_vmm_unmap(void* ptr, size_t bytes);
+int dl_vmm_release(uint64_t handle);
+int dl_mc_granularity(int ndev, size_t bytes, size_t* gran);
+int dl_mc_create(int ndev, size_t bytes, uint64_t* handle, int* fd);
+int dl_mc_add_device(uint64_t handle, int dev);
+int dl_mc_bind(uint64_t mc_handle, uint64_t mem_handle, size_t bytes);
+int dl_mc_unbind(uint64_t mc_handle, int dev, size_t bytes);
+int dl_ipc_alloc(int dev, size_t bytes, void** ptr, void* handle64);
+int dl_ipc_open(int dev, const void* handle64, void** ptr);
+int dl_ipc_close(void* ptr);
+int dl_ipc_free(void* ptr);
+int dl_enable_peer(int dev, int peer);
+int dl_can_access_peer(int dev, int peer, int* can);
+int dl_memset_sync(int dev, void* ptr, int value, size_t bytes);
+/* unix-domain-socket fd passing (SCM_RIGHTS) used to move VMM handles between local ranks */
+int dl_uds_listen(const char* name, int* sock);
+int dl_uds_send_fd(const char* name, int fd, int tag, int timeout_ms);
+int dl_uds_recv_fd(int sock, int* fd, int* tag, int timeout_ms);
+int dl_uds_close(int sock);
+int dl_close_fd(int fd);
+
+/* ---- collectives (all offsets are byte offsets into the symmetric heap) ---- */
+
+/* In-place all-reduce(sum) of n elements at heap offset `off`.  With
+ * scale_by_inv_active != 0 the f32 result is divided by the number of ranks
+ * that passed active != 0 (lua/AllReduceSGD.lua:20-27); inactive ranks
+ * contribute zeros (the drain all-reduce of lua/AllReduceSGD.lua:37).
+ * `payload` (31 bits) is published to every peer together with `active`. */
+int dl_allreduce(const dl_comm_t* c, int dtype, uint64_t off, uint64_t n, int variant, int active,
+                 uint32_t payload, int scale_by_inv_active, int nblocks, int channel, void* stream);
+
+/* Fused gradient all-reduce + 1/n_active + (momentum, weight decay) SGD update
+ * + parameter all-gather: grads at g_off are summed over active ranks, the
+ * owner of each slice updates params at p_off and pushes the new slice to every
+ * rank; grads are zeroed afterwards when zero_grads != 0.
+ * Replaces lua/AllReduceSGD.lua:18-30 followed by examples/cifar10.lua:187-191. */
+int dl_fused_sgd(const dl_comm_t* c, uint64_t g_off, uint64_t p_off, uint64_t m_off, uint64_t n,
+                 float lr, float momentum, float weight_decay, int nesterov, int variant,
+                 int active, uint32_t payload, int zero_grads, int nblocks, int channel,
+                 void* stream);
+
+/* Fused elastic averaging (lua/AllReduceEA.lua:34-45): c_new = c + sum_i a(x_i - c) is computed by
+ * the slice owner from peers' x and written to every replica at cnew_off, then
+ * x -= a (x - c_old) locally.  One launch. */
+int dl_fused_ea(const dl_comm_t* c, uint64_t x_off, uint64_t c_off, uint64_t cnew_off, uint64_t n,
+                float alpha, int variant, int active, uint32_t payload, int nblocks, int channel,
+                void* stream);
+
+/* Broadcast n floats at `off` from `root` to every rank (tree.scatter,
+ * lua/AllReduceSGD.lua:52, and the winner broadcast :43-47); when off2 != 0 the
+ * same values are also written at off2 (EA: center <- params,
+ * lua/AllReduceEA.lua:93-99). */
+int dl_broadcast(const dl_comm_t* c, uint64_t off, uint64_t off2, uint64_t n, int root, int variant,
+                 uint32_t payload, int nblocks, int channel, void* stream);
+
+/* A barrier only: publishes payload/active, fills dl_result. */
+int dl_barrier(const dl_comm_t* c, int active, uint32_t payload, int channel, void* stream);
+
+/* Copy the dl_result of `channel` to host (synchronises `stream`). */
+int dl_read_result(const dl_comm_t* c, int channel, dl_result_t* out, void* stream);
+/* Zero this rank's signal pad (call on every rank, then barrier on the host). */
+int dl_reset_pad(const dl_comm_t* c);
+
+/* ---- asynchronous EASGD (lua/AsyncEA.lua) ---- */
+/* Client side of one sync (lua/AsyncEA.lua:134-146 and :163-228 on the server):
+ * c = center on `server`'s heap (P2P loads), d = alpha (x - c), x -= d (local),
+ * center += d (red.add over NVLink).  exclusive != 0 serialises clients with a
+ * ticket lock in the server's pad (the recvAny mutex, lua/AsyncEA.lua:163-177).
+ * x is a plain device pointer; the center lives at c_off in the server heap. */
+int dl_async_ea_client(const dl_comm_t* c, int server, float* x, uint64_t c_off, uint64_t n,
+                       float alpha, int exclusive, int nblocks, void* stream);
+/* Copy n floats from `src_rank`'s heap at off into dst (P2P loads): initClient /
+ * startTest center pull (lua/AsyncEA.lua:64-78, :268-285). */
+int dl_peer_pull(const dl_comm_t* c, int src_rank, uint64_t off, float* dst, uint64_t n,
+                 int nblocks, void* stream);
+/* Read the server's sync counter (number of completed client syncs). */
+int dl_async_sync_count(const dl_comm_t* c, int server, uint64_t* count, void* stream);
+
+/* Host-visible 64-bit mailbox words in rank `rank`'s pad (index < 16): the tester handshake
+ * "Test?"/"Ack" (lua/AsyncEA.lua:239-258,268-292) and ready/done flags travel here. */
+int dl_mailbox_write(const dl_comm_t* c, int rank, int index, uint64_t value, void* stream);
+int dl_mailbox_read(const dl_comm_t* c, int rank, int index, uint64_t* value, void* stream);
+
+/* ---- local flat-vector ops (single GPU, no communication) ---- */
+/* p -= lr * (g*scale [+ wd*p] [momentum]); optionally zero g. world==1 fast path. */
+int dl_local_sgd(float* p, float* g, float* m, uint64_t n, float lr, float momentum,
+                 float weight_decay, int nesterov, float grad_scale, int zero_grads, void* stream);
+/* x -= alpha (x - c); c += world_scale * alpha (x_old - c)  (single-rank EA step) */
+int dl_local_ea(float* x, float* c, uint64_t n, float alpha, void* stream);
+/* Deterministic sum of (a[i]-b[i])^2 (b may be NULL) into out[0] (double).
+ * scratch: caller-provided device buffer of dl_sumsq_scratch_bytes() bytes,
+ * zero-initialised once; the kernel leaves it ready for the next call. */
+size_t dl_sumsq_scratch_bytes(void);
+int dl_sumsq_diff(const float* a, const float* b, uint64_t n, double* out, void* scratch,
+                  void* stream);
+/* 10x10-style confusion matrix accumulation: mat[target][argmax(logits)] += 1 */
+int dl_confusion_add(const float* logits, const int64_t* target, int batch, int classes,
+                     int64_t* mat, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DISTLEARN_B200_H */

@@ -1,0 +1,40 @@
+"""CIFAR-10 convnet of examples/Model.lua:20-66 (identical in examples/cifar10.lua:108-156).
+
+4 x [conv 5x5 pad 2 -> SpatialBatchNormalization(eps 1e-3) -> ReLU -> maxpool 2x2/2] with channels
+3->64->128->256->512, Reshape(2048), Linear 2048->10, LogSoftMax + ClassNLLCriterion.
+4,328,970 fp32 parameters (16.5 MiB) in 18 tensors; BatchNorm running statistics are buffers, not
+parameters, so — as in the reference — they are never synchronised between nodes."""
+from __future__ import annotations
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+
+class CifarConvNet(nn.Module):
+    CHANNELS = (3, 64, 128, 256, 512)
+
+    def __init__(self):
+        super().__init__()
+        convs, bns = [], []
+        for cin, cout in zip(self.CHANNELS[:-1], self.CHANNELS[1:]):
+            convs.append(nn.Conv2d(cin, cout, 5, 1, 2))            # examples/Model.lua:20,26,32,38
+            bns.append(nn.BatchNorm2d(cout, eps=1e-3))             # :21,27,33,39
+        self.convs = nn.ModuleList(convs)
+        self.bns = nn.ModuleList(bns)
+        self.linear = nn.Linear(512 * 2 * 2, 10)                   # :44-45
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        for conv, bn in zip(self.convs, self.bns):
+            x = F.max_pool2d(F.relu(bn(conv(x))), 2, 2)            # :59-61
+        x = self.linear(x.reshape(x.shape[0], 2048))               # :63
+        return F.log_softmax(x, dim=1)                             # :64
+
+
+def cifar_convnet(seed: int = 0) -> CifarConvNet:
+    """``torch.manualSeed(0)`` on every node before construction (examples/Model.lua:17)."""
+    gen_state = torch.random.get_rng_state()
+    torch.manual_seed(seed)
+    m = CifarConvNet()
+    torch.random.set_rng_state(gen_state)
+    return m

@@ -1,0 +1,672 @@
+"""Communicators: the transport layer under AllReduceSGD / AllReduceEA / AsyncEA.
+
+The reference's transport is ``ipc.Tree`` / ``ipc.LocalhostTree`` (a k-ary TCP tree:
+test/test_AllReduceSGD.lua:7, examples/mnist.lua:16).  Here a communicator owns a *symmetric
+heap* — the same buffer layout on every rank, each rank's heap addressable by all the others —
+and runs single-launch collectives over it:
+
+* :class:`P2PCommunicator`   — CUDA: heaps are VMM allocations mapped across processes over
+  NVLink (multicast/NVLS when the fabric exposes it, cudaIpc as fallback); collectives are the
+  sm_100a kernels in ``csrc/``.
+* :class:`HostCommunicator`  — CPU: heaps live in one POSIX shared-memory segment; the same
+  algorithms run in C++ (``csrc/host_transport.cpp``).
+* :class:`EmulatedCommunicator` — all ranks on ONE GPU, one cooperative launch plays every rank;
+  used to test the multi-rank kernels on a single-GPU box.
+
+``rank`` is 0-based; ``node_index`` (= rank + 1) is the reference's 1-based ``nodeIndex``.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import json
+import os
+import threading
+import uuid
+from dataclasses import dataclass
+from typing import List, Optional, Sequence
+
+import torch
+
+from .. import _lib
+from .._lib import DL_PAD_BYTES, DlComm, DlResult, VARIANT_NAMES, VARIANT_NVLS, VARIANT_ONESHOT, VARIANT_TWOSHOT
+
+_ALIGN = 512  # byte alignment of every symmetric allocation (>= 16 for 128-bit access)
+
+_DTYPE_CODES = {torch.float32: _lib.DT_F32, torch.int32: _lib.DT_I32, torch.int64: _lib.DT_I64,
+                torch.float64: _lib.DT_F64}
+
+
+@dataclass
+class CommResult:
+    """What a collective's arrival barrier learned (lua/AllReduceSGD.lua:20: ``_, n = allReduce``)."""
+    n_active: int
+    payloads: List[int]
+
+
+class SymBuffer:
+    """A symmetric allocation: same offset in every rank's heap; ``tensor`` is the local view."""
+
+    def __init__(self, comm: "Communicator", offset: int, numel: int, dtype: torch.dtype, tensor: torch.Tensor,
+                 name: str = ""):
+        self.comm, self.offset, self.numel, self.dtype, self.tensor, self.name = comm, offset, numel, dtype, tensor, name
+
+    @property
+    def nbytes(self) -> int:
+        return self.numel * self.tensor.element_size()
+
+    def sub(self, start: int, numel: int) -> "SymBuffer":
+        """A view of ``numel`` elements starting at element ``start`` (must keep 16-byte alignment)."""
+        es = self.tensor.element_size()
+        if (start * es) % 16 or start < 0 or start + numel > self.numel:
+            raise ValueError("SymBuffer.sub: range must be inside the buffer and 16-byte aligned")
+        return SymBuffer(self.comm, self.offset + start * es, numel, self.dtype, self.tensor[start:start + numel], self.name)
+
+    def __repr__(self) -> str:
+        return f"SymBuffer({self.name!r}, off={self.offset}, numel={self.numel}, dtype={self.dtype})"
+
+
+def _round_up(x: int, a: int) -> int:
+    return (x + a - 1) // a * a
+
+
+class _VariantTable:
+    """Message-size -> algorithm variant, per op.  Defaults are replaced by the measured table
+    that ``bench/sweep.py`` writes (``variant_table.json``); ``DL_B200_VARIANT`` forces one."""
+
+    DEFAULT = {"allreduce": 512 * 1024, "fused_sgd": 512 * 1024, "broadcast": 256 * 1024}
+
+    def __init__(self):
+        self.oneshot_max = dict(self.DEFAULT)
+        self.nvls_min = {"allreduce": 0, "fused_sgd": 0, "fused_ea": 0, "broadcast": 0}
+        path = os.environ.get("DL_B200_VARIANT_TABLE") or os.path.join(os.path.dirname(__file__), "variant_table.json")
+        if os.path.exists(path):
+            try:
+                data = json.load(open(path))
+                self.oneshot_max.update(data.get("oneshot_max", {}))
+                self.nvls_min.update(data.get("nvls_min", {}))
+            except Exception:
+                pass
+        self.forced = os.environ.get("DL_B200_VARIANT")
+
+    def pick(self, op: str, nbytes: int, world: int, has_mc: bool, requested: str = "auto") -> int:
+        req = self.forced or requested
+        if req and req != "auto":
+            v = VARIANT_NAMES[req]
+            if v == VARIANT_NVLS and not has_mc:
+                v = VARIANT_TWOSHOT
+            if op == "fused_ea" and v == VARIANT_ONESHOT:
+                v = VARIANT_TWOSHOT
+            return v
+        if op != "fused_ea" and nbytes <= self.oneshot_max.get(op, 0):
+            return VARIANT_ONESHOT
+        if has_mc and world > 2 and nbytes >= self.nvls_min.get(op, 0):
+            return VARIANT_NVLS
+        return VARIANT_TWOSHOT
+
+
+class Communicator:
+    """Common front end; subclasses supply the heap and the native calls."""
+
+    backend = "abstract"
+
+    def __init__(self, rank: int, world: int, device: torch.device, heap_bytes: int):
+        if not (1 <= world <= _lib.DL_MAX_RANKS):
+            raise ValueError(f"world size {world} unsupported (1..{_lib.DL_MAX_RANKS}: one NVSwitch domain)")
+        self.rank, self.world, self.device = rank, world, device
+        self.node_index, self.num_nodes = rank + 1, world
+        self.heap_bytes = heap_bytes
+        self._cursor = DL_PAD_BYTES
+        self._variants = _VariantTable()
+        self.launches = 0  # native collective launches issued through this communicator
+        self.max_blocks = int(os.environ.get("DL_B200_MAX_BLOCKS", "0"))
+
+    # -- allocation -------------------------------------------------------------------------------
+    def _local_bytes(self) -> torch.Tensor:  # uint8 view of the whole local heap
+        raise NotImplementedError
+
+    def alloc(self, numel: int, dtype: torch.dtype = torch.float32, name: str = "") -> SymBuffer:
+        """Symmetric allocation — every rank must call alloc in the same order with the same sizes."""
+        es = torch.empty((), dtype=dtype).element_size()
+        nbytes = _round_up(max(numel, 1) * es, 16)
+        off = _round_up(self._cursor, _ALIGN)
+        if off + nbytes > self.heap_bytes:
+            raise MemoryError(f"symmetric heap exhausted: need {off + nbytes} bytes, have {self.heap_bytes} "
+                              f"(raise heap_mb when creating the communicator)")
+        self._cursor = off + nbytes
+        t = self._local_bytes()[off:off + numel * es].view(dtype)
+        t.zero_()
+        return SymBuffer(self, off, numel, dtype, t, name)
+
+    def padded(self, numel: int) -> int:
+        """Round an element count up so that float4 access and slicing stay aligned."""
+        return _round_up(max(numel, 4), 32)
+
+    # -- results ------------------------------------------------------------------------------------
+    def _mk_result(self, res: DlResult) -> CommResult:
+        return CommResult(int(res.n_active), [int(res.payload[r]) for r in range(self.world)])
+
+    def pick_variant(self, op: str, nbytes: int, requested: str = "auto") -> int:
+        return self._variants.pick(op, nbytes, self.world, self.has_multicast, requested)
+
+    has_multicast = False
+
+    def close(self) -> None:
+        pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+
+# =====================================================================================================
+# CPU: POSIX shared memory
+# =====================================================================================================
+class HostCommunicator(Communicator):
+    """Same-host CPU ranks over one shared-memory segment (``csrc/host_transport.cpp``).
+
+    Replaces ``ipc.LocalhostTree(nodeIndex, numNodes)`` for CPU jobs (examples/mnist.lua:16)."""
+
+    backend = "host"
+
+    def __init__(self, rank: int, world: int, name: str, heap_mb: float = 64, timeout_s: float = 60.0):
+        heap_bytes = _round_up(int(heap_mb * (1 << 20)) + DL_PAD_BYTES, 4096)
+        super().__init__(rank, world, torch.device("cpu"), heap_bytes)
+        self._lib = _lib.host()
+        self._name = ("/" + name.strip("/")).encode()
+        h = C.c_void_p()
+        _lib.check_host(self._lib.dlh_open(self._name, rank, world, heap_bytes, float(timeout_s), C.byref(h)))
+        self._h = h
+        base = self._lib.dlh_base(h, rank)
+        self._bytes = torch.frombuffer((C.c_char * heap_bytes).from_address(base), dtype=torch.uint8)
+        self._res = DlResult()
+        self._closed = False
+
+    def _local_bytes(self) -> torch.Tensor:
+        return self._bytes
+
+    def set_timeout(self, seconds: float) -> None:
+        self._lib.dlh_set_timeout(self._h, float(seconds))
+
+    def barrier(self, active: int = 1, payload: int = 0, channel: int = 0, read: bool = True) -> CommResult:
+        _lib.check_host(self._lib.dlh_barrier(self._h, int(active), int(payload), channel, C.byref(self._res)))
+        return self._mk_result(self._res)
+
+    def allreduce(self, buf: SymBuffer, n: Optional[int] = None, active: int = 1, payload: int = 0,
+                  normalize: bool = False, variant: str = "auto", channel: int = 0, read: bool = True):
+        n = buf.numel if n is None else n
+        self.launches += 1
+        _lib.check_host(self._lib.dlh_allreduce(self._h, _DTYPE_CODES[buf.dtype], buf.offset, n, int(active), int(payload),
+                                                int(normalize), channel, C.byref(self._res)))
+        return self._mk_result(self._res)
+
+    def fused_sgd(self, grads: SymBuffer, params: SymBuffer, momentum_buf: Optional[SymBuffer], n: int, lr: float,
+                  momentum: float = 0.0, weight_decay: float = 0.0, nesterov: bool = False, active: int = 1,
+                  payload: int = 0, zero_grads: bool = True, variant: str = "auto", channel: int = 0, read: bool = True):
+        self.launches += 1
+        _lib.check_host(self._lib.dlh_fused_sgd(self._h, grads.offset, params.offset, momentum_buf.offset if momentum_buf else 0,
+                                                n, lr, momentum, weight_decay, int(nesterov), int(active), int(payload),
+                                                int(zero_grads), channel, C.byref(self._res)))
+        return self._mk_result(self._res)
+
+    def fused_ea(self, x: SymBuffer, c_cur: SymBuffer, c_next: SymBuffer, n: int, alpha: float, active: int = 1,
+                 payload: int = 0, variant: str = "auto", channel: int = 0, read: bool = True):
+        self.launches += 1
+        _lib.check_host(self._lib.dlh_fused_ea(self._h, x.offset, c_cur.offset, c_next.offset, n, alpha, int(active),
+                                               int(payload), channel, C.byref(self._res)))
+        return self._mk_result(self._res)
+
+    def broadcast(self, buf: SymBuffer, n: Optional[int] = None, root: int = 0, also: Optional[SymBuffer] = None,
+                  payload: int = 0, variant: str = "auto", channel: int = 0, read: bool = True):
+        n = buf.numel if n is None else n
+        self.launches += 1
+        _lib.check_host(self._lib.dlh_broadcast(self._h, buf.offset, also.offset if also else 0, n, root, int(payload),
+                                                channel, C.byref(self._res)))
+        return self._mk_result(self._res)
+
+    def read_result(self, channel: int = 0) -> CommResult:
+        return self._mk_result(self._res)
+
+    # async EASGD primitives
+    def async_client_sync(self, server: int, x: torch.Tensor, center: SymBuffer, n: int, alpha: float, exclusive: bool = False):
+        assert x.dtype == torch.float32 and x.is_contiguous() and x.device.type == "cpu"
+        self.launches += 1
+        _lib.check_host(self._lib.dlh_async_ea_client(self._h, server, x.data_ptr(), center.offset, n, alpha, int(exclusive)))
+
+    def peer_pull(self, src_rank: int, buf: SymBuffer, dst: torch.Tensor, n: Optional[int] = None):
+        n = buf.numel if n is None else n
+        assert dst.dtype == torch.float32 and dst.is_contiguous()
+        _lib.check_host(self._lib.dlh_peer_pull(self._h, src_rank, buf.offset, dst.data_ptr(), n))
+
+    def sync_count(self, server: int) -> int:
+        v = C.c_uint64()
+        _lib.check_host(self._lib.dlh_async_sync_count(self._h, server, C.byref(v)))
+        return int(v.value)
+
+    def mailbox_write(self, rank: int, index: int, value: int) -> None:
+        _lib.check_host(self._lib.dlh_mailbox_write(self._h, rank, index, int(value)))
+
+    def mailbox_read(self, rank: int, index: int) -> int:
+        v = C.c_uint64()
+        _lib.check_host(self._lib.dlh_mailbox_read(self._h, rank, index, C.byref(v)))
+        return int(v.value)
+
+    def synchronize(self) -> None:
+        pass
+
+    def close(self) -> None:
+        if not self._closed:
+            self._closed = True
+            self._bytes = None
+            self._lib.dlh_close(self._h, 1 if self.rank == 0 else 0)
+
+
+# =====================================================================================================
+# CUDA: symmetric heap over NVLink
+# =====================================================================================================
+class _CudaMem:
+    """Exposes a raw device range through __cuda_array_interface__ so torch can alias it."""
+
+    def __init__(self, ptr: int, nbytes: int):
+        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 2,
+                                         "strides": None}
+
+
+def _stream_ptr(device: torch.device, stream: Optional[torch.cuda.Stream] = None) -> int:
+    s = stream if stream is not None else torch.cuda.current_stream(device)
+    return s.cuda_stream
+
+
+class _CudaOps(Communicator):
+    """Native-call layer shared by the real and the emulated CUDA communicators."""
+
+    def __init__(self, rank, world, device, heap_bytes):
+        super().__init__(rank, world, device, heap_bytes)
+        self._lib = _lib.cuda()
+        self._c = DlComm()
+        self._c.rank, self._c.world, self._c.emulate = rank, world, 0
+        self._c.timeout_ns = int(float(os.environ.get("DL_B200_TIMEOUT_S", "20")) * 1e9)
+        self._res = DlResult()
+
+    def _nb(self, nblocks: int) -> int:
+        return nblocks if nblocks else self.max_blocks
+
+    def set_timeout(self, seconds: float) -> None:
+        self._c.timeout_ns = int(seconds * 1e9)
+
+    def barrier(self, active: int = 1, payload: int = 0, channel: int = 0, read: bool = True, stream=None):
+        with torch.cuda.device(self.device):
+            _lib.check(self._lib.dl_barrier(C.byref(self._c), int(active), int(payload), channel, _stream_ptr(self.device, stream)))
+            self.launches += 1
+            return self.read_result(channel, stream) if read else None
+
+    def allreduce(self, buf: SymBuffer, n: Optional[int] = None, active: int = 1, payload: int = 0,
+                  normalize: bool = False, variant: str = "auto", channel: int = 0, read: bool = False, nblocks: int = 0,
+                  stream=None):
+        n = buf.numel if n is None else n
+        nbytes = n * buf.tensor.element_size()
+        v = self.pick_variant("allreduce", nbytes, variant)
+        if buf.dtype != torch.float32 and v != VARIANT_ONESHOT:
+            v = VARIANT_ONESHOT
+        with torch.cuda.device(self.device):
+            _lib.check(self._lib.dl_allreduce(C.byref(self._c), _DTYPE_CODES[buf.dtype], buf.offset, n, v, int(active),
+                                              int(payload), int(normalize), self._nb(nblocks), channel,
+                                              _stream_ptr(self.device, stream)))
+            self.launches += 1
+            return self.read_result(channel, stream) if read else None
+
+    def fused_sgd(self, grads: SymBuffer, params: SymBuffer, momentum_buf: Optional[SymBuffer], n: int, lr: float,
+                  momentum: float = 0.0, weight_decay: float = 0.0, nesterov: bool = False, active: int = 1,
+                  payload: int = 0, zero_grads: bool = True, variant: str = "auto", channel: int = 0, read: bool = False,
+                  nblocks: int = 0, stream=None):
+        v = self.pick_variant("fused_sgd", n * 4, variant)
+        with torch.cuda.device(self.device):
+            _lib.check(self._lib.dl_fused_sgd(C.byref(self._c), grads.offset, params.offset,
+                                              momentum_buf.offset if momentum_buf else 0, n, lr, momentum, weight_decay,
+                                              int(nesterov), v, int(active), int(payload), int(zero_grads),
+                                              self._nb(nblocks), channel, _stream_ptr(self.device, stream)))
+            self.launches += 1
+            return self.read_result(channel, stream) if read else None
+
+    def fused_ea(self, x: SymBuffer, c_cur: SymBuffer, c_next: SymBuffer, n: int, alpha: float, active: int = 1,
+                 payload: int = 0, variant: str = "auto", channel: int = 0, read: bool = False, nblocks: int = 0,
+                 stream=None):
+        v = self.pick_variant("fused_ea", n * 4, variant)
+        with torch.cuda.device(self.device):
+            _lib.check(self._lib.dl_fused_ea(C.byref(self._c), x.offset, c_cur.offset, c_next.offset, n, alpha, v,
+                                             int(active), int(payload), self._nb(nblocks), channel,
+                                             _stream_ptr(self.device, stream)))
+            self.launches += 1
+            return self.read_result(channel, stream) if read else None
+
+    def broadcast(self, buf: SymBuffer, n: Optional[int] = None, root: int = 0, also: Optional[SymBuffer] = None,
+                  payload: int = 0, variant: str = "auto", channel: int = 0, read: bool = False, nblocks: int = 0,
+                  stream=None):
+        n = buf.numel if n is None else n
+        v = self.pick_variant("broadcast", n * 4, variant)
+        with torch.cuda.device(self.device):
+            _lib.check(self._lib.dl_broadcast(C.byref(self._c), buf.offset, also.offset if also else 0, n, root, v,
+                                              int(payload), self._nb(nblocks), channel, _stream_ptr(self.device, stream)))
+            self.launches += 1
+            return self.read_result(channel, stream) if read else None
+
+    def read_result(self, channel: int = 0, stream=None) -> CommResult:
+        """Host-synchronising read of the last collective's result words on ``channel``."""
+        with torch.cuda.device(self.device):
+            _lib.check(self._lib.dl_read_result(C.byref(self._c), channel, C.byref(self._res), _stream_ptr(self.device, stream)))
+        return self._mk_result(self._res)
+
+    def async_client_sync(self, server: int, x: torch.Tensor, center: SymBuffer, n: int, alpha: float,
+                          exclusive: bool = False, nblocks: int = 0, stream=None):
+        assert x.dtype == torch.float32 and x.is_contiguous() and x.is_cuda
+        with torch.cuda.device(self.device):
+            _lib.check(self._lib.dl_async_ea_client(C.byref(self._c), server, x.data_ptr(), center.offset, n, alpha,
+                                                    int(exclusive), self._nb(nblocks), _stream_ptr(self.device, stream)))
+        self.launches += 1
+
+    def peer_pull(self, src_rank: int, buf: SymBuffer, dst: torch.Tensor, n: Optional[int] = None, stream=None):
+        n = buf.numel if n is None else n
+        assert dst.dtype == torch.float32 and dst.is_contiguous() and dst.is_cuda
+        with torch.cuda.device(self.device):
+            _lib.check(self._lib.dl_peer_pull(C.byref(self._c), src_rank, buf.offset, dst.data_ptr(), n, 0,
+                                              _stream_ptr(self.device, stream)))
+        self.launches += 1
+
+    def sync_count(self, server: int) -> int:
+        v = C.c_uint64()
+        with torch.cuda.device(self.device):
+            _lib.check(self._lib.dl_async_sync_count(C.byref(self._c), server, C.byref(v), _stream_ptr(self.device)))
+        return int(v.value)
+
+    def mailbox_write(self, rank: int, index: int, value: int) -> None:
+        with torch.cuda.device(self.device):
+            _lib.check(self._lib.dl_mailbox_write(C.byref(self._c), rank, index, int(value), _stream_ptr(self.device)))
+
+    def mailbox_read(self, rank: int, index: int) -> int:
+        v = C.c_uint64()
+        with torch.cuda.device(self.device):
+            _lib.check(self._lib.dl_mailbox_read(C.byref(self._c), rank, index, C.byref(v), _stream_ptr(self.device)))
+        return int(v.value)
+
+    def synchronize(self) -> None:
+        torch.cuda.synchronize(self.device)
+
+
+class P2PCommunicator(_CudaOps):
+    """One process per GPU; heaps mapped across processes (VMM + fd passing, multicast if
+    available, cudaIpc fallback).  ``torch.distributed`` is used ONLY to bootstrap (exchange
+    handles, host barriers) — no collective on the training path goes through it."""
+
+    backend = "p2p"
+
+    def __init__(self, rank: Optional[int] = None, world: Optional[int] = None, device: Optional[torch.device] = None,
+                 heap_mb: float = 256, mode: str = "auto", use_multicast: Optional[bool] = None, group=None):
+        import torch.distributed as dist
+        if world is None:
+            world = dist.get_world_size(group) if dist.is_initialized() else 1
+        if rank is None:
+            rank = dist.get_rank(group) if dist.is_initialized() else 0
+        if device is None:
+            device = torch.device("cuda", torch.cuda.current_device())
+        if not torch.cuda.is_available():
+            raise RuntimeError("P2PCommunicator needs a CUDA device; use HostCommunicator on CPU")
+        self._dist, self._group = dist, group
+        heap_bytes = _round_up(int(heap_mb * (1 << 20)) + DL_PAD_BYTES, 2 << 20)
+        super().__init__(rank, world, device, heap_bytes)
+        self.mode = "local"
+        self._mem_handle = None
+        self._mc_handle = None
+        self._mapped: List[tuple] = []
+        self._ipc_ptrs: List[int] = []
+        dev = device.index if device.index is not None else torch.cuda.current_device()
+        self._dev = dev
+        torch.cuda.set_device(dev)
+        if use_multicast is None:
+            use_multicast = os.environ.get("DL_B200_DISABLE_NVLS", "0") != "1"
+        if world == 1:
+            self._heap_tensor = torch.zeros(heap_bytes, dtype=torch.uint8, device=device)
+            self._c.base[0] = self._heap_tensor.data_ptr()
+            self._bytes = self._heap_tensor
+        else:
+            if not dist.is_initialized():
+                raise RuntimeError("torch.distributed must be initialised to bootstrap a multi-rank P2PCommunicator")
+            self._bootstrap(mode, use_multicast)
+        _lib.check(self._lib.dl_reset_pad(C.byref(self._c)))
+        self._host_barrier()
+
+    # -- bootstrap ----------------------------------------------------------------------------------
+    def _host_barrier(self):
+        if self.world > 1:
+            torch.cuda.synchronize(self.device)
+            self._dist.barrier(group=self._group)
+
+    def _all_gather_obj(self, obj):
+        out = [None] * self.world
+        self._dist.all_gather_object(out, obj, group=self._group)
+        return out
+
+    def _bootstrap(self, mode: str, use_multicast: bool):
+        lib, dev = self._lib, self._dev
+        vmm, fdh, mc = C.c_int(0), C.c_int(0), C.c_int(0)
+        caps_ok = lib.dl_device_caps(dev, C.byref(vmm), C.byref(fdh), C.byref(mc)) == 0
+        mine = {"vmm": bool(caps_ok and vmm.value and fdh.value), "mc": bool(caps_ok and mc.value), "dev": dev,
+                "host": os.uname().nodename, "pid": os.getpid()}
+        caps = self._all_gather_obj(mine)
+        if len({c["host"] for c in caps}) != 1:
+            raise RuntimeError("P2PCommunicator spans one host (one NVSwitch domain); use the dist backend across hosts")
+        want_vmm = mode in ("auto", "vmm") and all(c["vmm"] for c in caps)
+        want_mc = want_vmm and use_multicast and all(c["mc"] for c in caps)
+        self.caps = caps
+        ok = False
+        if want_vmm:
+            try:
+                self._bootstrap_vmm(want_mc)
+                ok = True
+            except Exception as e:  # noqa: BLE001 - fall back collectively below
+                self._vmm_error = repr(e)
+                ok = False
+            oks = self._all_gather_obj(ok)
+            if not all(oks):
+                if mode == "vmm":
+                    raise RuntimeError(f"VMM heap bootstrap failed: {getattr(self, '_vmm_error', oks)}")
+                self._teardown_vmm()
+                ok = False
+        if not ok:
+            self._bootstrap_ipc()
+
+    def _bootstrap_vmm(self, want_mc: bool):
+        lib, dev = self._lib, self._dev
+        gran = C.c_size_t(0)
+        _lib.check(lib.dl_vmm_granularity(dev, C.byref(gran)))
+        g = max(int(gran.value), 2 << 20)
+        if want_mc:
+            mg = C.c_size_t(0)
+            if lib.dl_mc_granularity(self.world, _round_up(self.heap_bytes, g), C.byref(mg)) == 0 and mg.value:
+                g = max(g, int(mg.value))
+            else:
+                want_mc = False
+        self.heap_bytes = _round_up(self.heap_bytes, g)
+        job = self._all_gather_obj(uuid.uuid4().hex[:12])[0]
+        handle, fd = C.c_uint64(0), C.c_int(-1)
+        _lib.check(lib.dl_vmm_alloc(dev, self.heap_bytes, C.byref(handle), C.byref(fd)))
+        self._mem_handle = int(handle.value)
+        sock = C.c_int(-1)
+        name = lambda r: f"dlb200-{job}-{r}".encode()  # noqa: E731
+        _lib.check(lib.dl_uds_listen(name(self.rank), C.byref(sock)))
+        self._dist.barrier(group=self._group)  # every listener is up
+
+        received, errors = {}, []
+        expect = (self.world - 1) + (1 if (want_mc and self.rank != 0) else 0)
+
+        def receiver():
+            try:
+                for _ in range(expect):
+                    rfd, tag = C.c_int(-1), C.c_int(-1)
+                    _lib.check(lib.dl_uds_recv_fd(sock.value, C.byref(rfd), C.byref(tag), 60000))
+                    received[int(tag.value)] = int(rfd.value)
+            except Exception as e:  # noqa: BLE001
+                errors.append(e)
+
+        th = threading.Thread(target=receiver, daemon=True)
+        th.start()
+        mc_handle, mc_fd = C.c_uint64(0), C.c_int(-1)
+        mc_ok = want_mc
+        if want_mc and self.rank == 0:
+            if lib.dl_mc_create(self.world, self.heap_bytes, C.byref(mc_handle), C.byref(mc_fd)) != 0:
+                mc_ok = False
+                self._mc_error = lib.dl_last_error().decode()
+        for p in range(self.world):
+            if p != self.rank:
+                _lib.check(lib.dl_uds_send_fd(name(p), fd.value, self.rank, 60000))
+                if want_mc and self.rank == 0:
+                    # tag 1000 = multicast handle (or tag 1001 with a dummy fd when creation failed)
+                    _lib.check(lib.dl_uds_send_fd(name(p), mc_fd.value if mc_ok else fd.value, 1000 if mc_ok else 1001, 60000))
+        th.join()
+        lib.dl_uds_close(sock.value)
+        if errors:
+            raise errors[0]
+        # map every heap
+        for p in range(self.world):
+            ptr = C.c_void_p()
+            if p == self.rank:
+                _lib.check(lib.dl_vmm_map(dev, self._mem_handle, self.heap_bytes, C.byref(ptr)))
+                self._mapped.append((ptr.value, self.heap_bytes, None))
+            else:
+                h = C.c_uint64(0)
+                _lib.check(lib.dl_vmm_import(received[p], C.byref(h)))
+                lib.dl_close_fd(received[p])
+                _lib.check(lib.dl_vmm_map(dev, h.value, self.heap_bytes, C.byref(ptr)))
+                self._mapped.append((ptr.value, self.heap_bytes, int(h.value)))
+            self._c.base[p] = ptr.value
+        lib.dl_close_fd(fd.value)
+        self._bytes = torch.as_tensor(_CudaMem(self._c.base[self.rank], self.heap_bytes), device=self.device)
+        self.mode = "vmm"
+        # multicast (NVLS)
+        if want_mc:
+            if self.rank == 0:
+                mch = int(mc_handle.value) if mc_ok else None
+            else:
+                if 1000 in received:
+                    h = C.c_uint64(0)
+                    mc_ok = lib.dl_vmm_import(received[1000], C.byref(h)) == 0
+                    lib.dl_close_fd(received[1000])
+                    mch = int(h.value) if mc_ok else None
+                else:
+                    if 1001 in received:
+                        lib.dl_close_fd(received[1001])
+                    mc_ok, mch = False, None
+            if mc_ok:
+                mc_ok = lib.dl_mc_add_device(mch, dev) == 0
+            mc_ok = all(self._all_gather_obj(bool(mc_ok)))
+            if mc_ok:
+                mc_ok = lib.dl_mc_bind(mch, self._mem_handle, self.heap_bytes) == 0
+                if not mc_ok:
+                    self._mc_error = lib.dl_last_error().decode()
+            mc_ok = all(self._all_gather_obj(bool(mc_ok)))
+            if mc_ok:
+                ptr = C.c_void_p()
+                mc_ok = lib.dl_vmm_map(dev, mch, self.heap_bytes, C.byref(ptr)) == 0
+                mc_ok = all(self._all_gather_obj(bool(mc_ok)))
+                if mc_ok:
+                    self._c.mc = ptr.value
+                    self._mc_handle = mch
+                    self.has_multicast = True
+        self._bytes.zero_()
+        torch.cuda.synchronize(self.device)
+
+    def _teardown_vmm(self):
+        for ptr, nbytes, h in self._mapped:
+            self._lib.dl_vmm_unmap(ptr, nbytes)
+            if h is not None:
+                self._lib.dl_vmm_release(h)
+        self._mapped = []
+        if self._mem_handle is not None:
+            self._lib.dl_vmm_release(self._mem_handle)
+            self._mem_handle = None
+        self._c.mc = None
+        self.has_multicast = False
+
+    def _bootstrap_ipc(self):
+        lib, dev = self._lib, self._dev
+        ptr = C.c_void_p()
+        handle = (C.c_char * 64)()
+        _lib.check(lib.dl_ipc_alloc(dev, self.heap_bytes, C.byref(ptr), handle))
+        self._ipc_local = ptr.value
+        handles = self._all_gather_obj(bytes(handle.raw))
+        for p in range(self.world):
+            if p == self.rank:
+                self._c.base[p] = ptr.value
+            else:
+                q = C.c_void_p()
+                buf = (C.c_char * 64).from_buffer_copy(handles[p])
+                _lib.check(lib.dl_ipc_open(dev, buf, C.byref(q)))
+                self._ipc_ptrs.append(q.value)
+                self._c.base[p] = q.value
+        self._bytes = torch.as_tensor(_CudaMem(ptr.value, self.heap_bytes), device=self.device)
+        self._bytes.zero_()
+        torch.cuda.synchronize(self.device)
+        self.mode = "ipc"
+
+    def _local_bytes(self) -> torch.Tensor:
+        return self._bytes
+
+    def describe(self) -> dict:
+        return {"backend": self.backend, "mode": self.mode, "world": self.world, "rank": self.rank,
+                "heap_bytes": self.heap_bytes, "multicast": bool(self.has_multicast),
+                "mc_error": getattr(self, "_mc_error", None), "vmm_error": getattr(self, "_vmm_error", None)}
+
+    def close(self) -> None:
+        # Mappings are released by process exit; explicit teardown keeps long-lived processes clean.
+        try:
+            torch.cuda.synchronize(self.device)
+        except Exception:  # noqa: BLE001
+            pass
+
+
+class EmulatedCommunicator(_CudaOps):
+    """All ``world`` ranks on ONE GPU: each rank has its own heap (a torch allocation) and every
+    collective is one cooperative launch with gridDim.y = world.  ``active`` arguments are
+    bitmasks over ranks, rank r publishes ``payload + r``.  Test-only."""
+
+    backend = "emulated"
+
+    def __init__(self, world: int, device: Optional[torch.device] = None, heap_mb: float = 16):
+        device = device or torch.device("cuda", torch.cuda.current_device())
+        heap_bytes = _round_up(int(heap_mb * (1 << 20)) + DL_PAD_BYTES, 4096)
+        super().__init__(0, world, device, heap_bytes)
+        self._c.emulate = 1
+        self.heaps = [torch.zeros(heap_bytes, dtype=torch.uint8, device=device) for _ in range(world)]
+        for r in range(world):
+            self._c.base[r] = self.heaps[r].data_ptr()
+        _lib.check(self._lib.dl_reset_pad(C.byref(self._c)))
+
+    def _local_bytes(self) -> torch.Tensor:
+        return self.heaps[0]
+
+    def alloc_all(self, numel: int, dtype: torch.dtype = torch.float32, name: str = ""):
+        """Returns (SymBuffer, [tensor of rank 0, tensor of rank 1, ...])."""
+        buf = self.alloc(numel, dtype, name)
+        es = buf.tensor.element_size()
+        views = [h[buf.offset:buf.offset + numel * es].view(dtype) for h in self.heaps]
+        for v in views:
+            v.zero_()
+        return buf, views
+
+    def result_of(self, rank: int, channel: int = 0) -> CommResult:
+        self._c.rank = rank
+        try:
+            return self.read_result(channel)
+        finally:
+            self._c.rank = 0
+
+
+def create_communicator(backend: str = "auto", **kw) -> Communicator:
+    """``backend``: 'p2p' (CUDA, default when a GPU is present), 'host' (CPU shared memory)."""
+    if backend == "auto":
+        backend = "p2p" if torch.cuda.is_available() else "host"
+    if backend == "p2p":
+        return P2PCommunicator(**kw)
+    if backend == "host":
+        return HostCommunicator(**kw)
+    raise ValueError(f"unknown backend {backend!r}")
