@@ -1,0 +1,224 @@
+#!/usr/bin/env python
+"""Headline benchmark: CIFAR-10 convnet (examples/Model.lua) AllReduceSGD training throughput.
+
+    python bench.py --gpus N --steps K --warmup W            # this framework (fused sm_100a path)
+    python bench.py --impl nccl ...                          # torch.distributed NCCL baseline
+    python bench.py --impl reference ...                     # the reference itself (Lua/Torch7: unavailable here)
+
+For N > 1 launch with ``python -m torch.distributed.run --nnodes=1 --nproc-per-node N ...``.
+Metric: samples/s over the whole job; synthetic CIFAR-shaped data, random-init weights, fp32 (the
+reference casts everything to float, examples/cifar10.lua:136), per-GPU batch fixed (weak
+scaling).  ``value`` is device-timed (CUDA events, max over ranks) with the batch already on the
+device; ``e2e`` goes through the public TrainStep.step() API and includes, every step, the H2D
+copy of that step's batch from pinned host memory and the D2H read of the loss.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+
+def parse():
+    p = argparse.ArgumentParser()
+    p.add_argument("--gpus", type=int, default=1)
+    p.add_argument("--steps", type=int, default=100)
+    p.add_argument("--warmup", type=int, default=10)
+    p.add_argument("--impl", choices=["ours", "nccl", "reference"], default="ours")
+    p.add_argument("--per-gpu-batch", type=int, default=128, help="examples/AsyncEASGD.sh:39 uses 128 per GPU")
+    p.add_argument("--lr", type=float, default=0.1, help="examples/cifar10.lua:7")
+    p.add_argument("--graph", type=int, default=1, help="capture the step in a CUDA graph (ours)")
+    p.add_argument("--tf32", type=int, default=0, help="allow TF32 convolutions (default: strict fp32 like the reference)")
+    p.add_argument("--variant", default="auto")
+    p.add_argument("--nblocks", type=int, default=0)
+    p.add_argument("--heap-mb", type=float, default=128)
+    return p.parse_args()
+
+
+def reference_arm(args) -> None:
+    # The reference is pure Lua/Torch7 (0 Python files, rockspec build type "builtin"); the offline pip
+    # install of /root/reference fails for lack of a Python project, and the image has no lua/luajit/th
+    # (DESIGN.md "Reference arm").
+    print(json.dumps({"impl": "reference",
+                      "unavailable": "reference is Lua/Torch7 + luarocks ipc: not pip-installable, no lua/th runtime in the image"}))
+
+
+def main() -> None:
+    args = parse()
+    if args.impl == "reference":
+        reference_arm(args)
+        return
+
+    import torch
+    import torch.distributed as dist
+    import torch.nn.functional as F
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus and world > 1:
+        args.gpus = world
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a GPU (use examples/mnist.py --backend host for the CPU configuration)")
+    dev = torch.device("cuda", local_rank)
+    torch.cuda.set_device(dev)
+    torch.backends.cudnn.allow_tf32 = bool(args.tf32)
+    torch.backends.cuda.matmul.allow_tf32 = bool(args.tf32)
+    torch.backends.cudnn.benchmark = True
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("MASTER_PORT", "29500")
+        if args.impl == "nccl":
+            dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+        else:
+            dist.init_process_group("gloo", rank=rank, world_size=world)  # bootstrap only
+
+    from torch_distlearn_b200.models import cifar_convnet
+    from torch_distlearn_b200.utils.timing import ClockSampler, max_over_ranks
+
+    B = args.per_gpu_batch
+    model = cifar_convnet().to(dev)
+    K, W = args.steps, max(args.warmup, 3)
+    # a pool of distinct pinned host batches, cycled: every step copies a fresh batch
+    pool = 8
+    g = torch.Generator().manual_seed(1234 + rank)
+    host_x = [torch.randn(B, 3, 32, 32, generator=g).pin_memory() for _ in range(pool)]
+    host_y = [torch.randint(0, 10, (B,), generator=g).pin_memory() for _ in range(pool)]
+    dev_x = [t.to(dev) for t in host_x]
+    dev_y = [t.to(dev) for t in host_y]
+    h2d_bytes = host_x[0].numel() * 4 + host_y[0].numel() * 8
+    d2h_bytes = 4
+    launches = 0
+
+    if args.impl == "ours":
+        import torch_distlearn_b200 as dl
+        from torch_distlearn_b200.parallel.trainer import TrainStep
+        comm = dl.P2PCommunicator(rank=rank, world=world, device=dev, heap_mb=args.heap_mb)
+        flat = dl.FlatParams(comm, model)
+        sgd = dl.AllReduceSGD(comm, flat)
+        sgd.synchronizeParameters()
+        step = TrainStep(model, flat, sgd, (B, 3, 32, 32), lr=args.lr, use_graph=bool(args.graph), variant=args.variant,
+                         nblocks=args.nblocks)
+        step.capture()
+
+        def run_dev(i):
+            step.load(dev_x[i % pool], dev_y[i % pool])
+            step.run()
+
+        def run_e2e(i):
+            step.step(host_x[i % pool], host_y[i % pool])
+            return step.loss_value()
+
+        describe = comm.describe()
+    else:
+        from baseline.nccl_algos import NcclAllReduceSGD, NcclFlat
+        flat = NcclFlat(model)
+        algo = NcclAllReduceSGD(flat)
+        algo.synchronize_parameters()
+        x_static = torch.zeros(B, 3, 32, 32, device=dev)
+        y_static = torch.zeros(B, dtype=torch.int64, device=dev)
+        loss_dev = torch.zeros((), device=dev)
+        loss_host = torch.zeros(()).pin_memory()
+
+        def body():
+            out = model(x_static)
+            loss = F.nll_loss(out, y_static)
+            loss.backward()
+            loss_dev.copy_(loss.detach())
+            algo.step(args.lr)
+
+        def run_dev(i):
+            x_static.copy_(dev_x[i % pool], non_blocking=True)
+            y_static.copy_(dev_y[i % pool], non_blocking=True)
+            body()
+
+        def run_e2e(i):
+            x_static.copy_(host_x[i % pool], non_blocking=True)
+            y_static.copy_(host_y[i % pool], non_blocking=True)
+            body()
+            loss_host.copy_(loss_dev, non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+            return float(loss_host)
+
+        describe = {"backend": "nccl"}
+
+    def barrier():
+        torch.cuda.synchronize(dev)
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    # ---- device-timed region -------------------------------------------------------------------
+    for i in range(W):
+        run_dev(i)
+    barrier()
+    sampler = ClockSampler(gpu_index=local_rank, period_ms=100).start() if rank == 0 else None
+    if args.impl == "ours":
+        l0 = comm.launches
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for i in range(K):
+        run_dev(i)
+    e1.record()
+    barrier()
+    ms = e0.elapsed_time(e1)
+    if args.impl == "ours":
+        launches = comm.launches - l0
+    ms = max_over_ranks(ms, world)
+    # ---- end-to-end region (public API, H2D + D2H every step) -------------------------------------
+    for i in range(3):
+        run_e2e(i)
+    barrier()
+    t0 = time.perf_counter()
+    e2, e3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e2.record()
+    last = 0.0
+    for i in range(K):
+        last = run_e2e(i)
+    e3.record()
+    barrier()
+    e2e_ms = max_over_ranks(max(e2.elapsed_time(e3), 0.0), world)
+    wall_ms = max_over_ranks((time.perf_counter() - t0) * 1e3, world)
+    clocks = sampler.stop() if sampler is not None else None
+
+    if rank == 0:
+        total = B * world
+        value = total * K / (ms / 1e3)
+        e2e_value = total * K / (max(e2e_ms, 1e-9) / 1e3)
+        base = None
+        try:
+            with open(os.path.join(ROOT, "baseline", "measured.json")) as f:
+                base = json.load(f).get("cifar_sgd_samples_per_s", {}).get(str(world))
+        except Exception:
+            base = None
+        out = {
+            "metric": "CIFAR-10 convnet AllReduceSGD training throughput", "value": round(value, 1), "unit": "samples/s",
+            "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": round(ms / K, 4), "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": (round(value / base, 4) if base else None), "dtype": "fp32",
+            "data": "synthetic CIFAR-shaped 3x32x32, random-init weights", "impl": args.impl,
+            "config": {"model": "cifar10_convnet (examples/Model.lua, 4,328,970 params)", "global_batch": total,
+                       "per_gpu_batch": B, "seq_len": None, "parallelism": f"dp{world}", "lr": args.lr,
+                       "tf32": bool(args.tf32), "cuda_graph": bool(args.graph) if args.impl == "ours" else False,
+                       "l2": "no explicit flush: each step streams >126 MB of activations/gradients (working set > L2)",
+                       "transport": describe},
+            "e2e": {"value": round(e2e_value, 1), "unit": "samples/s", "h2d_bytes_per_step": h2d_bytes,
+                    "d2h_bytes_per_step": d2h_bytes, "ms_per_step": round(e2e_ms / K, 4),
+                    "wall_ms_per_step": round(wall_ms / K, 4), "last_loss": round(last, 5)},
+            "gpu_launches": int(launches),
+            "clocks": clocks,
+        }
+        print(json.dumps(out))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,114 @@
+"""TrainStep — the whole synchronous training step as ONE CUDA-graph replay.
+
+    host batch (pinned) --H2D--> static input --> forward --> loss --> backward (grads land in the
+    flat symmetric gradient buffer) --> fused all-reduce + 1/n + SGD + param all-gather kernel
+
+The reference's step is ``df(params, x, y)`` -> ``sumAndNormalizeGradients(grads)`` -> a Lua loop of
+``p:add(-lr, g)`` (examples/cifar10.lua:181-191): dozens of small launches plus a socket tree.
+Here the forward/backward kernels (cuDNN/cuBLAS through PyTorch) and the fused collective kernel are
+captured once and replayed, so a step costs one graph launch on the host; the cross-GPU barriers
+inside the collective are device-side flags with device-side epochs, which is what makes the
+kernel capturable.  Every rank must replay the same number of steps between synchronisation points
+(use ``AllReduceSGD.synchronizeParameters`` / the eager path for uneven partitions).
+"""
+from __future__ import annotations
+
+from typing import Callable, Optional, Tuple
+
+import torch
+import torch.nn.functional as F
+
+from .allreduce_sgd import AllReduceSGD
+from .flat import FlatParams
+
+
+class TrainStep:
+    def __init__(self, model: torch.nn.Module, flat: FlatParams, sgd: AllReduceSGD, batch_shape: Tuple[int, ...],
+                 lr: float, momentum: float = 0.0, weight_decay: float = 0.0, nesterov: bool = False,
+                 loss_fn: Optional[Callable] = None, use_graph: bool = True, variant: str = "auto",
+                 target_dtype: torch.dtype = torch.int64, warmup: int = 3, nblocks: int = 0):
+        self.model, self.flat, self.sgd = model, flat, sgd
+        self.lr, self.momentum, self.weight_decay, self.nesterov = lr, momentum, weight_decay, nesterov
+        self.loss_fn = loss_fn or F.nll_loss          # the models end in log_softmax (ClassNLLCriterion)
+        self.variant, self.nblocks = variant, nblocks
+        dev = flat.device
+        self.device = dev
+        self.x = torch.zeros(batch_shape, dtype=torch.float32, device=dev)
+        self.y = torch.zeros(batch_shape[0], dtype=target_dtype, device=dev)
+        self.loss = torch.zeros((), dtype=torch.float32, device=dev)
+        self.logits: Optional[torch.Tensor] = None
+        self.loss_host = torch.zeros((), dtype=torch.float32).pin_memory() if dev.type == "cuda" else torch.zeros(())
+        self.graph: Optional[torch.cuda.CUDAGraph] = None
+        self.launches_per_step = 0
+        self.use_graph = bool(use_graph and dev.type == "cuda")
+        self._warmup = warmup
+        self._captured = False
+
+    # ------------------------------------------------------------------------------------------------
+    def _body(self) -> None:
+        out = self.model(self.x)
+        loss = self.loss_fn(out, self.y)
+        loss.backward()
+        self.logits = out.detach()
+        self.loss.copy_(loss.detach())
+        self.sgd.step(self.flat, lr=self.lr, momentum=self.momentum, weight_decay=self.weight_decay,
+                      nesterov=self.nesterov, zero_grads=True, variant=self.variant, nblocks=self.nblocks)
+
+    def _eager(self) -> None:
+        before = self.sgd.comm.launches
+        self._body()
+        self.launches_per_step = self.sgd.comm.launches - before
+
+    def capture(self) -> None:
+        """Warm up eagerly (loads modules, lets cuDNN pick algorithms), then capture one step."""
+        if self._captured:
+            return
+        self._captured = True
+        self.flat.attach_grads()
+        if not self.use_graph:
+            return
+        side = torch.cuda.Stream(self.device)
+        side.wait_stream(torch.cuda.current_stream(self.device))
+        with torch.cuda.stream(side):
+            for _ in range(max(self._warmup, 1)):
+                self._eager()
+        torch.cuda.current_stream(self.device).wait_stream(side)
+        torch.cuda.synchronize(self.device)
+        self.graph = torch.cuda.CUDAGraph()
+        steps_before = self.sgd.steps
+        with torch.cuda.graph(self.graph):
+            self._body()
+        # the capture itself did not execute a step
+        self.sgd.steps = steps_before
+        torch.cuda.synchronize(self.device)
+
+    # ------------------------------------------------------------------------------------------------
+    def load(self, x: torch.Tensor, y: torch.Tensor) -> None:
+        """Copy a batch into the static input buffers (async H2D when the source is pinned)."""
+        self.x.copy_(x, non_blocking=True)
+        self.y.copy_(y, non_blocking=True)
+
+    def run(self) -> torch.Tensor:
+        """One training step on whatever is in the static buffers; returns the (device) loss."""
+        if not self._captured:
+            self.capture()
+        if self.graph is not None:
+            self.graph.replay()
+            self.sgd.steps += 1
+            self.sgd.comm.launches += self.launches_per_step
+        else:
+            self._eager()
+        return self.loss
+
+    def step(self, x: torch.Tensor, y: torch.Tensor) -> torch.Tensor:
+        """The user-facing call: load a (host or device) batch, run the step, return the device loss."""
+        self.load(x, y)
+        return self.run()
+
+    def loss_value(self) -> float:
+        """Device->host read of the last step's loss (synchronises)."""
+        if self.device.type == "cuda":
+            self.loss_host.copy_(self.loss, non_blocking=True)
+            torch.cuda.current_stream(self.device).synchronize()
+            return float(self.loss_host)
+        return float(self.loss)
