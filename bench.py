@@ -87,9 +87,12 @@ def main() -> None:
     K, W = args.steps, max(args.warmup, 3)
     # a pool of distinct pinned host batches, cycled: every step copies a fresh batch
     pool = 8
-    g = torch.Generator().manual_seed(1234 + rank)
-    host_x = [torch.randn(B, 3, 32, 32, generator=g).pin_memory() for _ in range(pool)]
-    host_y = [torch.randint(0, 10, (B,), generator=g).pin_memory() for _ in range(pool)]
+    from torch_distlearn_b200.utils.data import cifar_dataset
+    ds = cifar_dataset(partition=rank + 1, partitions=world, num_samples=pool * B * world)
+    get_batch, _ = ds.sampledBatcher(B, "label-uniform")      # examples/cifar10.lua:53-54
+    batches = [get_batch() for _ in range(pool)]
+    host_x = [b.input.contiguous().pin_memory() for b in batches]
+    host_y = [b.target.contiguous().pin_memory() for b in batches]
     dev_x = [t.to(dev) for t in host_x]
     dev_y = [t.to(dev) for t in host_y]
     h2d_bytes = host_x[0].numel() * 4 + host_y[0].numel() * 8

@@ -179,9 +179,12 @@ def test_async_ea_conserves_mass(exclusive):
     total = sum(o.double() for o in outs)
     want = 1.0 + sum(float(r + 1) for r in range(1, world))
     torch.testing.assert_close(total, torch.full((n,), want, dtype=torch.float64), rtol=1e-5, atol=1e-5)
-    # elements are all treated alike
-    for o in outs:
-        assert float(o.max() - o.min()) < 1e-5
+    # with the mutex every sync sees a whole center, so all elements are treated alike; lock-free
+    # syncs may read a center that another client is half-way through updating (torn reads are
+    # part of the contract), so only conservation holds there
+    if exclusive:
+        for o in outs:
+            assert float(o.max() - o.min()) < 1e-5
 
 
 def _w_timeout(rank, world, job):

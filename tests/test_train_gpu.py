@@ -63,7 +63,7 @@ def test_graph_replay_equals_eager():
     for use_graph in (False, True):
         dl, comm, model, ref, flat = _setup(cifar_convnet)
         sgd = dl.AllReduceSGD(comm, flat)
-        step = TrainStep(model, flat, sgd, (16, 3, 32, 32), lr=0.05, use_graph=use_graph, warmup=2)
+        step = TrainStep(model, flat, sgd, (16, 3, 32, 32), lr=0.002, use_graph=use_graph, warmup=2)
         step.capture()
         g = torch.Generator().manual_seed(3)
         losses = []
@@ -74,9 +74,10 @@ def test_graph_replay_equals_eager():
             losses.append(step.loss_value())
         results.append((losses, flat.params.tensor.clone(), comm.launches))
     (l_e, p_e, n_e), (l_g, p_g, n_g) = results
-    # eager does no warm-up steps; the graph path warms up twice on zero inputs: compare trends, not bits
-    assert l_e[-1] < l_e[0] and l_g[-1] < l_g[0]
-    assert n_e == 6 and n_g == 6 + 2
+    # both paths do the same 2 warm-up steps and the same 6 steps: replay must reproduce eager
+    assert n_e == n_g == 6 + 2
+    torch.testing.assert_close(torch.tensor(l_g), torch.tensor(l_e), rtol=2e-2, atol=2e-2)
+    torch.testing.assert_close(p_g, p_e, rtol=1e-2, atol=1e-3)
     assert torch.isfinite(p_g).all()
 
 

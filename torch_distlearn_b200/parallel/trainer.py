@@ -60,12 +60,13 @@ class TrainStep:
         self.launches_per_step = self.sgd.comm.launches - before
 
     def capture(self) -> None:
-        """Warm up eagerly (loads modules, lets cuDNN pick algorithms), then capture one step."""
+        """Warm up eagerly on the current contents of the static buffers (loads modules, lets cuDNN
+        pick algorithms; these ARE real training steps), then capture one step when graphs are on."""
         if self._captured:
             return
         self._captured = True
         self.flat.attach_grads()
-        if not self.use_graph:
+        if self.device.type != "cuda":
             return
         side = torch.cuda.Stream(self.device)
         side.wait_stream(torch.cuda.current_stream(self.device))
@@ -74,6 +75,8 @@ class TrainStep:
                 self._eager()
         torch.cuda.current_stream(self.device).wait_stream(side)
         torch.cuda.synchronize(self.device)
+        if not self.use_graph:
+            return
         self.graph = torch.cuda.CUDAGraph()
         steps_before = self.sgd.steps
         with torch.cuda.graph(self.graph):
