@@ -66,7 +66,7 @@ def run_sgd_fused_uneven(comm, rank, world, seed=1, epochs=2, n=1000) -> Dict[st
             sgd.step(lr=0.1 / (1 + epoch), momentum=0.5)
         winner = sgd.synchronizeParameters()
     comm.synchronize()
-    return {"params": flat.params.tensor[:n].cpu(), "grads_max": float(flat.grads.tensor.abs().max()), "winner": winner}
+    return {"params": flat.params.tensor[:n].cpu().clone(), "grads_max": float(flat.grads.tensor.abs().max()), "winner": winner}
 
 
 def verify_sgd_fused_uneven(results, world, seed=1, epochs=2, n=1000) -> None:

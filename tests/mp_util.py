@@ -50,15 +50,28 @@ def run_ranks(fn: Callable, world: int, *args: Any, timeout: float = 120.0) -> L
     for p in procs:
         p.start()
     results, errors = {}, []
+    import queue
+    import time
+    deadline = time.time() + timeout
     try:
-        for _ in range(world):
-            rank, status, out = q.get(timeout=timeout)
+        while len(results) + len(errors) < world:
+            try:
+                rank, status, out = q.get(timeout=0.5)
+            except queue.Empty:
+                dead = [(i, p.exitcode) for i, p in enumerate(procs) if p.exitcode not in (None, 0) and i not in results]
+                if dead:
+                    errors.append(f"rank(s) died without a result (rank, exit code): {dead}")
+                    break
+                if time.time() > deadline:
+                    errors.append(f"timeout after {timeout}s; finished ranks: {sorted(results)}")
+                    break
+                continue
             if status == "ok":
                 results[rank] = _unpack(out)
             else:
                 errors.append(f"rank {rank}: {out}")
-    except Exception as e:  # queue.Empty on timeout
-        errors.append(f"timeout/queue error: {e!r}")
+    except Exception as e:  # noqa: BLE001
+        errors.append(f"queue error: {e!r}")
     finally:
         for p in procs:
             p.join(timeout=5 if not errors else 1)

@@ -78,11 +78,11 @@ class TrainStep:
         if not self.use_graph:
             return
         self.graph = torch.cuda.CUDAGraph()
-        steps_before = self.sgd.steps
+        steps_before, launches_before = self.sgd.steps, self.sgd.comm.launches
         with torch.cuda.graph(self.graph):
             self._body()
         # the capture itself did not execute a step
-        self.sgd.steps = steps_before
+        self.sgd.steps, self.sgd.comm.launches = steps_before, launches_before
         torch.cuda.synchronize(self.device)
 
     # ------------------------------------------------------------------------------------------------
