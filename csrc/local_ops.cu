@@ -88,3 +88,65 @@ extern "C" int dl_confusion_add(const float* logits, const int64_t* target, int 
   DL_CUDA(cudaGetLastError());
   return DL_OK;
 }
+
+// ---- dl_sumsq_diff_static: the same reduction for callers that cannot allocate -----------------
+// Some hosts of this library have no way to hand dl_sumsq_diff() a scratch buffer: a job that
+// gave every byte of HBM to its own pool at start-up and treats any later driver allocation as a
+// bug (cudaMalloc can fail there, and it synchronises the whole device when it succeeds); a
+// metrics or watchdog thread that must not touch the allocator while the training thread owns
+// it; a plain-C trainer that links this .so without torch and so has no caching allocator to
+// borrow from.  For them the scratch lives in the library image itself: one fixed array per GPU,
+// resident from the moment the library is loaded on that GPU until the process exits.
+//
+// DL_SUMSQ_STATIC_SCRATCH_BYTES (2,560 bytes per GPU) is all there is.  It holds the partial sums
+// of the largest grid this reduction ever launches, and the entry point refuses vectors longer
+// than DL_SUMSQ_STATIC_MAX_N elements (include/distlearn_b200.h) instead of growing anything.
+#define DL_SUMSQ_STATIC_SCRATCH_BYTES 2560  // >= sizeof(SumsqScratch), multiple of 256
+static_assert(sizeof(SumsqScratch) <= DL_SUMSQ_STATIC_SCRATCH_BYTES, "static scratch too small");
+
+static __device__ __align__(256) unsigned char g_sumsq_static_scratch[DL_SUMSQ_STATIC_SCRATCH_BYTES];
+
+#include <mutex>
+
+// In host code `g_sumsq_static_scratch` is only a handle for the runtime, not an address the GPU
+// understands; the device address differs per GPU and is looked up once per device.
+static void* g_sumsq_static_ptr[64] = {nullptr};
+static std::mutex g_sumsq_static_mu;
+
+static int sumsq_static_scratch(void** out) {
+  int dev = -1;
+  DL_CUDA(cudaGetDevice(&dev));
+  DL_REQUIRE(dev >= 0 && dev < 64, "dl_sumsq_diff_static: device index %d out of range", dev);
+  std::lock_guard<std::mutex> lock(g_sumsq_static_mu);
+  if (g_sumsq_static_ptr[dev] == nullptr) {
+    void* p = nullptr;
+    DL_CUDA(cudaGetSymbolAddress(&p, g_sumsq_static_scratch));
+    DL_REQUIRE(p != nullptr, "dl_sumsq_diff_static: no device address for the static scratch on device %d", dev);
+    g_sumsq_static_ptr[dev] = p;
+  }
+  *out = g_sumsq_static_ptr[dev];
+  return DL_OK;
+}
+
+extern "C" size_t dl_sumsq_static_scratch_bytes(void) { return DL_SUMSQ_STATIC_SCRATCH_BYTES; }
+extern "C" uint64_t dl_sumsq_static_max_n(void) { return DL_SUMSQ_STATIC_MAX_N; }
+
+extern "C" int dl_sumsq_diff_static(const float* a, const float* b, uint64_t n, double* out, void* stream) {
+  DL_REQUIRE(a && out, "dl_sumsq_diff_static: null pointer");
+  DL_REQUIRE(n <= DL_SUMSQ_STATIC_MAX_N,
+             "dl_sumsq_diff_static: n = %llu exceeds the supported maximum of %llu elements; "
+             "use dl_sumsq_diff with a caller-provided scratch buffer",
+             (unsigned long long)n, (unsigned long long)DL_SUMSQ_STATIC_MAX_N);
+  const int nb = sumsq_blocks(n);  // <= DL_SUMSQ_BLOCKS, whose partial sums the array holds (static_assert above)
+  void* scratch = nullptr;
+  const int rc = sumsq_static_scratch(&scratch);
+  if (rc != DL_OK) return rc;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  // The array keeps whatever the previous call (or an aborted one) left behind.  The partial sums
+  // are overwritten before they are read; the arrival counter is the one word that must be zero.
+  SumsqScratch* s = static_cast<SumsqScratch*>(scratch);
+  DL_CUDA(cudaMemsetAsync(&s->arrived, 0, sizeof(s->arrived), st));
+  sumsq_diff_kernel<<<nb, DL_SUMSQ_THREADS, 0, st>>>(a, b, n, out, s);
+  DL_CUDA(cudaGetLastError());
+  return DL_OK;
+}

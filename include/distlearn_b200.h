@@ -170,6 +170,27 @@ int dl_local_ea(float* x, float* c, uint64_t n, float alpha, void* stream);
 size_t dl_sumsq_scratch_bytes(void);
 int dl_sumsq_diff(const float* a, const float* b, uint64_t n, double* out, void* scratch,
                   void* stream);
+/* dl_sumsq_diff for callers that cannot allocate device memory.  (No counterpart in the
+ * reference: it has no metrics kernels and no allocation-free mode.)
+ * Meant for hosts that cannot supply dl_sumsq_diff's scratch buffer: jobs that hand all of HBM to
+ * their own pool at start-up and forbid driver allocations afterwards, monitoring threads that
+ * must stay out of the allocator, C trainers that link this library without torch.  The scratch
+ * is a fixed dl_sumsq_static_scratch_bytes() = 2,560-byte array inside the library, held on every
+ * GPU that loads it until the process exits; nothing is allocated or freed by this call, by the
+ * CUDA runtime on its behalf, or by torch.  a, b (may be NULL) and out are the caller's.
+ *  - n may not exceed DL_SUMSQ_STATIC_MAX_N elements; larger calls fail with DL_EINVAL and a
+ *    message, and should use dl_sumsq_diff with their own scratch.
+ *  - The first call on each device (with that device current) looks up the array's device
+ *    address; make that first call before starting any stream capture.
+ *  - All calls on one GPU share the array.  Each call re-zeroes the one word that has to start at
+ *    zero and overwrites the rest before reading it, so stale contents are harmless; but two
+ *    calls that may run at the same time on the same GPU (different streams, different threads)
+ *    race on it and produce garbage.  Keep them on one stream or order them with events.
+ *  - Same arithmetic and block order as dl_sumsq_diff: results agree bit for bit. */
+#define DL_SUMSQ_STATIC_MAX_N (1ull << 31)
+size_t dl_sumsq_static_scratch_bytes(void);
+uint64_t dl_sumsq_static_max_n(void);
+int dl_sumsq_diff_static(const float* a, const float* b, uint64_t n, double* out, void* stream);
 /* 10x10-style confusion matrix accumulation: mat[target][argmax(logits)] += 1 */
 int dl_confusion_add(const float* logits, const int64_t* target, int batch, int classes,
                      int64_t* mat, void* stream);

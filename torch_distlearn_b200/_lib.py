@@ -110,6 +110,9 @@ def cuda():
     _sig(lib, "dl_sumsq_scratch_bytes", sz, [])
     _sig(lib, "dl_sumsq_diff", i32, [vp, vp, u64, vp, vp, vp])
     _sig(lib, "dl_confusion_add", i32, [vp, vp, i32, i32, vp, vp])
+    _sig(lib, "dl_sumsq_static_scratch_bytes", sz, [])
+    _sig(lib, "dl_sumsq_static_max_n", u64, [])
+    _sig(lib, "dl_sumsq_diff_static", i32, [vp, vp, u64, vp, vp])
     return lib
 
 
