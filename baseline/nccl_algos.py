@@ -53,8 +53,7 @@ class NcclAllReduceSGD:
     def step(self, lr: float, momentum: float = 0.0, momentum_buf: Optional[torch.Tensor] = None):
         g, p = self.flat.grads, self.flat.params
         if self.world > 1:
-            dist.all_reduce(g, group=self.group)
-            g.div_(self.world)
+            dist.all_reduce(g, op=dist.ReduceOp.AVG, group=self.group)   # NCCL divides in the reduction
         if momentum and momentum_buf is not None:
             momentum_buf.mul_(momentum).add_(g)
             p.add_(momentum_buf, alpha=-lr)

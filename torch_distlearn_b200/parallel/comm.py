@@ -75,13 +75,17 @@ class _VariantTable:
 
     DEFAULT = {"allreduce": 512 * 1024, "fused_sgd": 512 * 1024, "broadcast": 256 * 1024}
 
-    def __init__(self):
+    def __init__(self, world: int = 8):
         self.oneshot_max = dict(self.DEFAULT)
         self.nvls_min = {"allreduce": 0, "fused_sgd": 0, "fused_ea": 0, "broadcast": 0}
         path = os.environ.get("DL_B200_VARIANT_TABLE") or os.path.join(os.path.dirname(__file__), "variant_table.json")
         if os.path.exists(path):
             try:
                 data = json.load(open(path))
+                keys = sorted(int(k) for k in data if k.isdigit())
+                if keys:      # per-world tables: take the smallest measured world >= ours (else the largest)
+                    pick = next((k for k in keys if k >= world), keys[-1])
+                    data = data[str(pick)]
                 self.oneshot_max.update(data.get("oneshot_max", {}))
                 self.nvls_min.update(data.get("nvls_min", {}))
             except Exception:
@@ -116,7 +120,7 @@ class Communicator:
         self.node_index, self.num_nodes = rank + 1, world
         self.heap_bytes = heap_bytes
         self._cursor = DL_PAD_BYTES
-        self._variants = _VariantTable()
+        self._variants = _VariantTable(world)
         self.launches = 0  # native collective launches issued through this communicator
         self.max_blocks = int(os.environ.get("DL_B200_MAX_BLOCKS", "0"))
 
