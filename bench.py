@@ -38,6 +38,9 @@ def parse():
     p.add_argument("--variant", default="auto")
     p.add_argument("--nblocks", type=int, default=0)
     p.add_argument("--heap-mb", type=float, default=128)
+    p.add_argument("--bucket-mb", type=float, default=0.0,
+                   help="ours: launch the fused kernel per gradient bucket of this size, overlapped with backward (0 = one launch)")
+    p.add_argument("--bucket-blocks", type=int, default=32, help="CTAs per bucket launch (leaves the other SMs to cuDNN)")
     return p.parse_args()
 
 
@@ -107,7 +110,7 @@ def main() -> None:
         sgd = dl.AllReduceSGD(comm, flat)
         sgd.synchronizeParameters()
         step = TrainStep(model, flat, sgd, (B, 3, 32, 32), lr=args.lr, use_graph=bool(args.graph), variant=args.variant,
-                         nblocks=args.nblocks)
+                         nblocks=args.nblocks, bucket_mb=args.bucket_mb, bucket_blocks=args.bucket_blocks)
         step.capture()
 
         def run_dev(i):
@@ -229,7 +232,7 @@ def main() -> None:
             "data": "synthetic CIFAR-shaped 3x32x32, random-init weights", "impl": args.impl,
             "config": {"model": "cifar10_convnet (examples/Model.lua, 4,328,970 params)", "global_batch": total,
                        "per_gpu_batch": B, "seq_len": None, "parallelism": f"dp{world}", "lr": args.lr,
-                       "tf32": bool(args.tf32), "cuda_graph": bool(args.graph),
+                       "tf32": bool(args.tf32), "cuda_graph": bool(args.graph), "bucket_mb": args.bucket_mb,
                        "l2": "no explicit flush: each step streams >126 MB of activations/gradients (working set > L2)",
                        "transport": describe},
             "e2e": {"value": round(e2e_value, 1), "unit": "samples/s", "h2d_bytes_per_step": h2d_bytes,

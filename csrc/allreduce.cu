@@ -101,6 +101,57 @@ __global__ void __launch_bounds__(DL_THREADS, 1) allreduce_oneshot_kernel(dl_com
   }
 }
 
+// One pass over the owner's slice: reduce (kMc: in the switch; else P2P loads in rank order), scale,
+// and hand the result to every rank (kMc: multimem.st; else P2P stores).
+template <int W, int U, bool kMc>
+__device__ __forceinline__ void allreduce_slice_pass(const dl_comm_t& c, const ArArgs& a, const DlSlice& s, int world,
+                                                     uint32_t mask, float inv, unsigned long long tid0,
+                                                     unsigned long long stride) {
+  for (unsigned long long i0 = s.begin + tid0; i0 < s.end; i0 += stride * U) {
+    float4 acc[U];
+    if (kMc) {
+      const float4* mg = dl_mc_at<float4>(c, a.off);
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const unsigned long long idx = i0 + u * stride;
+        acc[u] = idx < s.end ? dl_mc_ld_reduce_f4(mg + idx) : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+    } else {
+      float4 v[U][W];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const unsigned long long idx = i0 + u * stride;
+#pragma unroll
+        for (int j = 0; j < W; ++j)
+          v[u][j] = (idx < s.end && j < world && ((mask >> j) & 1u)) ? dl_ld_f4(dl_at<float4>(c, j, a.off) + idx)
+                                                                    : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        acc[u] = v[u][0];
+#pragma unroll
+        for (int j = 1; j < W; ++j) acc[u] = acc[u] + v[u][j];
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const unsigned long long idx = i0 + u * stride;
+      if (idx < s.end) {
+        const float4 r = dl_scale(acc[u], inv);
+        if (kMc) {
+          dl_mc_st_f4(dl_mc_at<float4>(c, a.off) + idx, r);
+        } else {
+#pragma unroll
+          for (int j = 0; j < W; ++j)
+            if (j < world) dl_st_f4(dl_at<float4>(c, j, a.off) + idx, r);
+        }
+      }
+    }
+  }
+}
+
+#define DL_NVLS_U 8  // vectors in flight per thread on the multimem path (long switch round trip)
+
 template <int kWorld, bool kNvls, bool kEmu>
 __global__ void __launch_bounds__(DL_THREADS, 1) allreduce_twoshot_kernel(dl_comm_t c, ArArgs a) {
   __shared__ uint32_t pay[DL_MAX_RANKS];
@@ -123,47 +174,12 @@ __global__ void __launch_bounds__(DL_THREADS, 1) allreduce_twoshot_kernel(dl_com
 
   if (ok) {
     const float inv = (a.scale && n_act > 1) ? 1.f / static_cast<float>(n_act) : 1.f;
-    const bool all_active = (n_act == world);
-    for (unsigned long long i0 = s.begin + tid0; i0 < s.end; i0 += stride * U) {
-      float4 acc[U];
-      if (kNvls && all_active) {
-        const float4* mg = dl_mc_at<float4>(c, a.off);
-#pragma unroll
-        for (int u = 0; u < U; ++u) {
-          const unsigned long long idx = i0 + u * stride;
-          acc[u] = idx < s.end ? dl_mc_ld_reduce_f4(mg + idx) : make_float4(0.f, 0.f, 0.f, 0.f);
-        }
-      } else {
-        float4 v[U][W];
-#pragma unroll
-        for (int u = 0; u < U; ++u) {
-          const unsigned long long idx = i0 + u * stride;
-#pragma unroll
-          for (int j = 0; j < W; ++j)
-            v[u][j] = (idx < s.end && j < world && ((mask >> j) & 1u)) ? dl_ld_f4(dl_at<float4>(c, j, a.off) + idx)
-                                                                      : make_float4(0.f, 0.f, 0.f, 0.f);
-        }
-#pragma unroll
-        for (int u = 0; u < U; ++u) {
-          acc[u] = v[u][0];
-#pragma unroll
-          for (int j = 1; j < W; ++j) acc[u] = acc[u] + v[u][j];
-        }
-      }
-#pragma unroll
-      for (int u = 0; u < U; ++u) {
-        const unsigned long long idx = i0 + u * stride;
-        if (idx < s.end) {
-          const float4 r = dl_scale(acc[u], inv);
-          if (kNvls) {
-            dl_mc_st_f4(dl_mc_at<float4>(c, a.off) + idx, r);
-          } else {
-#pragma unroll
-            for (int j = 0; j < W; ++j)
-              if (j < world) dl_st_f4(dl_at<float4>(c, j, a.off) + idx, r);
-          }
-        }
-      }
+    if (kNvls && n_act == world) {
+      allreduce_slice_pass<W, DL_NVLS_U, true>(c, a, s, world, mask, inv, tid0, stride);
+    } else if (kNvls) {  // ranks are draining: leave their stale data out (P2P, rank order)
+      allreduce_slice_pass<W, 1, false>(c, a, s, world, mask, inv, tid0, stride);
+    } else {
+      allreduce_slice_pass<W, U, false>(c, a, s, world, mask, inv, tid0, stride);
     }
   }
   dl_block_barrier(c, rank, world, a.channel, 0u, pay);

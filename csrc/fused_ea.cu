@@ -30,7 +30,7 @@ template <int kWorld, bool kNvls, bool kEmu>
 __global__ void __launch_bounds__(DL_THREADS, 1) fused_ea_kernel(dl_comm_t c, EaArgs a) {
   __shared__ uint32_t pay[DL_MAX_RANKS];
   constexpr int W = kWorld ? kWorld : DL_MAX_RANKS;
-  constexpr int U = kWorld == 1 ? 8 : kWorld == 2 ? 8 : kWorld == 4 ? 4 : 2;
+  constexpr int U = kNvls ? 8 : kWorld == 1 ? 8 : kWorld == 2 ? 8 : kWorld == 4 ? 4 : 2;
   const int rank = kEmu ? static_cast<int>(blockIdx.y) : c.rank;
   const int world = kWorld ? kWorld : c.world;
   const int act = kEmu ? ((a.active >> rank) & 1u) : (a.active & 3u);

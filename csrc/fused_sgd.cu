@@ -47,6 +47,69 @@ __device__ __forceinline__ float4 sgd_update(float4 g, float4 p, float4* m_ptr, 
   return p;
 }
 
+// One pass over the owner's slice [s.begin, s.end): reduce the gradients of the active ranks
+// (kMc: one multimem.ld_reduce through the NVSwitch; else P2P loads summed in rank order), update
+// the owner's parameters and distribute them (kMc: one multimem.st; else P2P stores).
+// U = 16-byte vectors a thread keeps in flight per source.
+template <int W, int U, bool kMc>
+__device__ __forceinline__ void sgd_slice_pass(const dl_comm_t& c, const SgdArgs& a, const DlSlice& s, int rank, int world,
+                                               uint32_t mask, float inv, unsigned long long tid0,
+                                               unsigned long long stride) {
+  float4* p_loc = dl_at<float4>(c, rank, a.p_off);
+  float4* m_loc = a.m_off ? dl_at<float4>(c, rank, a.m_off) : nullptr;
+  for (unsigned long long i0 = s.begin + tid0; i0 < s.end; i0 += stride * U) {
+    float4 acc[U];
+    if (kMc) {
+      const float4* mg = dl_mc_at<float4>(c, a.g_off);
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const unsigned long long idx = i0 + u * stride;
+        acc[u] = idx < s.end ? dl_mc_ld_reduce_f4(mg + idx) : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+    } else {
+      float4 v[U][W];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const unsigned long long idx = i0 + u * stride;
+#pragma unroll
+        for (int j = 0; j < W; ++j) {
+          v[u][j] = (idx < s.end && j < world && ((mask >> j) & 1u))
+                        ? dl_ld_f4(dl_at<float4>(c, j, a.g_off) + idx)
+                        : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        acc[u] = v[u][0];
+#pragma unroll
+        for (int j = 1; j < W; ++j) acc[u] = acc[u] + v[u][j];
+      }
+    }
+    float4 pv[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const unsigned long long idx = i0 + u * stride;
+      if (idx < s.end) pv[u] = p_loc[idx];
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const unsigned long long idx = i0 + u * stride;
+      if (idx < s.end) {
+        const float4 pn = sgd_update(dl_scale(acc[u], inv), pv[u], m_loc ? m_loc + idx : nullptr, a);
+        if (kMc) {
+          dl_mc_st_f4(dl_mc_at<float4>(c, a.p_off) + idx, pn);
+        } else {
+#pragma unroll
+          for (int j = 0; j < W; ++j)
+            if (j < world) dl_st_f4(dl_at<float4>(c, j, a.p_off) + idx, pn);
+        }
+      }
+    }
+  }
+}
+
+#define DL_NVLS_U 8  // multimem.ld_reduce round trips through the switch are long: keep 128 B per thread in flight
+
 template <int kWorld, bool kNvls, bool kEmu>
 __global__ void __launch_bounds__(DL_THREADS, 1) sgd_twoshot_kernel(dl_comm_t c, SgdArgs a) {
   __shared__ uint32_t pay[DL_MAX_RANKS];
@@ -70,51 +133,14 @@ __global__ void __launch_bounds__(DL_THREADS, 1) sgd_twoshot_kernel(dl_comm_t c,
 
   if (ok && n_act > 0) {
     const float inv = n_act > 1 ? 1.f / static_cast<float>(n_act) : 1.f;
-    const bool all_active = (n_act == world);
-    float4* p_loc = dl_at<float4>(c, rank, a.p_off);
-    float4* m_loc = a.m_off ? dl_at<float4>(c, rank, a.m_off) : nullptr;
-    for (unsigned long long i0 = s.begin + tid0; i0 < s.end; i0 += stride * U) {
-      float4 acc[U];
-      if (kNvls && all_active) {
-        const float4* mg = dl_mc_at<float4>(c, a.g_off);
-#pragma unroll
-        for (int u = 0; u < U; ++u) {
-          const unsigned long long idx = i0 + u * stride;
-          acc[u] = idx < s.end ? dl_mc_ld_reduce_f4(mg + idx) : make_float4(0.f, 0.f, 0.f, 0.f);
-        }
-      } else {
-        float4 v[U][W];
-#pragma unroll
-        for (int u = 0; u < U; ++u) {
-          const unsigned long long idx = i0 + u * stride;
-#pragma unroll
-          for (int j = 0; j < W; ++j) {
-            v[u][j] = (idx < s.end && j < world && ((mask >> j) & 1u))
-                          ? dl_ld_f4(dl_at<float4>(c, j, a.g_off) + idx)
-                          : make_float4(0.f, 0.f, 0.f, 0.f);
-          }
-        }
-#pragma unroll
-        for (int u = 0; u < U; ++u) {
-          acc[u] = v[u][0];
-#pragma unroll
-          for (int j = 1; j < W; ++j) acc[u] = acc[u] + v[u][j];
-        }
-      }
-#pragma unroll
-      for (int u = 0; u < U; ++u) {
-        const unsigned long long idx = i0 + u * stride;
-        if (idx < s.end) {
-          const float4 pn = sgd_update(dl_scale(acc[u], inv), p_loc[idx], m_loc ? m_loc + idx : nullptr, a);
-          if (kNvls) {
-            dl_mc_st_f4(dl_mc_at<float4>(c, a.p_off) + idx, pn);
-          } else {
-#pragma unroll
-            for (int j = 0; j < W; ++j)
-              if (j < world) dl_st_f4(dl_at<float4>(c, j, a.p_off) + idx, pn);
-          }
-        }
-      }
+    if (kNvls && n_act == world) {
+      sgd_slice_pass<W, DL_NVLS_U, true>(c, a, s, rank, world, mask, inv, tid0, stride);
+    } else if (kNvls) {
+      // some ranks are draining: the switch would add their stale gradients too, so this (rare)
+      // round reads the active ranks over P2P and pushes the parameters with P2P stores
+      sgd_slice_pass<W, 1, false>(c, a, s, rank, world, mask, inv, tid0, stride);
+    } else {
+      sgd_slice_pass<W, U, false>(c, a, s, rank, world, mask, inv, tid0, stride);
     }
   }
   const bool ok2 = dl_block_barrier(c, rank, world, a.channel, 0u, pay);

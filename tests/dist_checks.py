@@ -229,10 +229,60 @@ def verify_tree_and_metrics(results, world) -> None:
         assert int(res["cm"].sum()) == 4 * world and int(res["cm"].diag().sum()) == 4 * world
 
 
+
+# ---- bucketed fused step (overlap with backward) == whole-vector fused step ----------------------------------
+def _mlp(seed):
+    torch.manual_seed(seed)
+    return torch.nn.Sequential(torch.nn.Linear(20, 64), torch.nn.Tanh(), torch.nn.Linear(64, 33), torch.nn.Tanh(),
+                               torch.nn.Linear(33, 10), torch.nn.LogSoftmax(dim=1))
+
+
+def run_sgd_bucketed(comm, rank, world, seed=5, epochs=2, use_graph=False) -> Dict[str, Any]:
+    import torch.nn.functional as F
+    import torch_distlearn_b200 as dl
+    from torch_distlearn_b200.parallel.trainer import TrainStep
+    dev = _dev(comm)
+    outs = {}
+    for mode, bucket_mb in (("whole", 0.0), ("bucketed", 0.001)):          # 0.001 MB -> ~260-element buckets
+        model = _mlp(seed).to(dev)
+        flat = dl.FlatParams(comm, model, with_momentum=True, name=mode)
+        sgd = dl.AllReduceSGD(comm, flat, channel=0)
+        sgd.synchronizeParameters()
+        step = TrainStep(model, flat, sgd, (8, 20), lr=0.05, momentum=0.9, weight_decay=1e-3, use_graph=use_graph,
+                         warmup=1, bucket_mb=bucket_mb, bucket_blocks=4)
+        if bucket_mb:
+            assert len(step.buckets.buckets) >= 3
+        for epoch in range(epochs):
+            steps = _steps_for(rank, epoch, 2, 5, seed) if not use_graph else 4
+            for s in range(steps):
+                g = torch.Generator().manual_seed(seed + 977 * epoch + 31 * s + rank)
+                x = torch.randn(8, 20, generator=g)
+                y = torch.randint(0, 10, (8,), generator=g)
+                step.step(x.to(dev), y.to(dev))
+            sgd.synchronizeParameters()
+        comm.synchronize()
+        outs[mode] = flat.params.tensor[:flat.numel].cpu().clone()
+        outs[mode + "_grads_max"] = float(flat.grads.tensor.abs().max())
+        if step.buckets is not None:
+            step.buckets.remove()
+    return outs
+
+
+def verify_sgd_bucketed(results, world, **_kw) -> None:
+    for r in range(world):
+        assert torch.equal(results[r]["whole"], results[0]["whole"])
+        assert torch.equal(results[r]["bucketed"], results[0]["bucketed"])
+        assert results[r]["whole_grads_max"] == 0.0 and results[r]["bucketed_grads_max"] == 0.0
+    # owner-computes with rank-order sums: the bucket geometry must not change a single bit
+    assert torch.equal(results[0]["whole"], results[0]["bucketed"])
+    assert torch.isfinite(results[0]["whole"]).all()
+
+
 SCENARIOS = {
     "sgd_reference_test": (run_sgd_reference_test, verify_sgd_reference_test),
     "sgd_fused_uneven": (run_sgd_fused_uneven, verify_sgd_fused_uneven),
     "ea_reference_test": (run_ea_reference_test, verify_ea_reference_test),
     "async_ea": (run_async_ea, verify_async_ea),
     "tree_and_metrics": (run_tree_and_metrics, verify_tree_and_metrics),
+    "sgd_bucketed": (run_sgd_bucketed, verify_sgd_bucketed),
 }

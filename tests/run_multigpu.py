@@ -143,13 +143,15 @@ def main():
                     kw = dict(exclusive=True, with_tester=False)
                 else:
                     kw = dict(exclusive=(world % 2 == 0), with_tester=True)
-            out = run(comm, rank, world, **kw)
-            comm.synchronize()
-            results = gather(out, world)
-            if rank == 0:
-                verify(results, world, **kw)
-                print(f"scenario {name}: ok", flush=True)
-            dist.barrier()
+            kws = [kw] if name != "sgd_bucketed" else [dict(use_graph=False), dict(use_graph=True)]
+            for kw in kws:
+                out = run(comm, rank, world, **kw)
+                comm.synchronize()
+                results = gather(out, world)
+                if rank == 0:
+                    verify(results, world, **kw)
+                    print(f"scenario {name} {kw if kw else ''}: ok", flush=True)
+                dist.barrier()
     except BaseException:  # noqa: BLE001
         ok = False
         print(f"[rank {rank}] FAILED\n{traceback.format_exc()}", flush=True)

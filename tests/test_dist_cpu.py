@@ -48,3 +48,9 @@ def test_async_ea_roles(world, exclusive, with_tester):
 
 def test_tree_facade_and_confusion_matrix():
     _run("tree_and_metrics", 3)
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_bucketed_step_equals_whole_vector_step(world):
+    """Per-bucket launches from autograd hooks (uneven steps, drain rounds) give bit-identical parameters."""
+    _run("sgd_bucketed", world)

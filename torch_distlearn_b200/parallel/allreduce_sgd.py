@@ -101,6 +101,8 @@ class AllReduceSGD:
         while True:
             if self._last is None:
                 res = self.comm.barrier(active=0, payload=payload, channel=self.channel, read=True)
+            elif self._last[0] == "bucketed":
+                res = self._last[1].drain_round()
             elif self._last[0] == "fused":
                 _, flat, n, kw = self._last
                 self.comm.fused_sgd(flat.grads, flat.params, flat.momentum if kw["momentum"] != 0.0 else None, n,

@@ -26,7 +26,8 @@ class TrainStep:
     def __init__(self, model: torch.nn.Module, flat: FlatParams, sgd: AllReduceSGD, batch_shape: Tuple[int, ...],
                  lr: float, momentum: float = 0.0, weight_decay: float = 0.0, nesterov: bool = False,
                  loss_fn: Optional[Callable] = None, use_graph: bool = True, variant: str = "auto",
-                 target_dtype: torch.dtype = torch.int64, warmup: int = 3, nblocks: int = 0):
+                 target_dtype: torch.dtype = torch.int64, warmup: int = 3, nblocks: int = 0, bucket_mb: float = 0.0,
+                 bucket_blocks: int = 32):
         self.model, self.flat, self.sgd = model, flat, sgd
         self.lr, self.momentum, self.weight_decay, self.nesterov = lr, momentum, weight_decay, nesterov
         self.loss_fn = loss_fn or F.nll_loss          # the models end in log_softmax (ClassNLLCriterion)
@@ -43,6 +44,13 @@ class TrainStep:
         self.use_graph = bool(use_graph and dev.type == "cuda")
         self._warmup = warmup
         self._captured = False
+        # bucket_mb > 0: launch the fused kernel per gradient bucket from autograd hooks, overlapped
+        # with the rest of backward on a side stream (parallel/bucketed.py)
+        self.buckets = None
+        if bucket_mb > 0:
+            from .bucketed import GradBuckets
+            self.buckets = GradBuckets(flat, sgd, bucket_mb=bucket_mb, nblocks=bucket_blocks, variant=variant)
+            self.buckets.set_hyper(lr, momentum, weight_decay, nesterov)
 
     # ------------------------------------------------------------------------------------------------
     def _body(self) -> None:
@@ -51,8 +59,11 @@ class TrainStep:
         loss.backward()
         self.logits = out.detach()
         self.loss.copy_(loss.detach())
-        self.sgd.step(self.flat, lr=self.lr, momentum=self.momentum, weight_decay=self.weight_decay,
-                      nesterov=self.nesterov, zero_grads=True, variant=self.variant, nblocks=self.nblocks)
+        if self.buckets is not None:
+            self.buckets.finish()           # the per-bucket kernels were launched from the backward hooks
+        else:
+            self.sgd.step(self.flat, lr=self.lr, momentum=self.momentum, weight_decay=self.weight_decay,
+                          nesterov=self.nesterov, zero_grads=True, variant=self.variant, nblocks=self.nblocks)
 
     def _eager(self) -> None:
         before = self.sgd.comm.launches
