@@ -1,0 +1,59 @@
+#!/usr/bin/env python
+"""Asynchronous EASGD — a worker (counterpart of examples/EASGD_client.lua).
+
+Loop order is the reference's (examples/EASGD_client.lua:106-117): gradient at x, then ``syncClient``
+(every ``--communicationTime`` steps: ONE kernel that loads the center from the server GPU, applies
+d = alpha (x - c), x -= d locally and adds d into the center with NVLink atomics), then the SGD step
+with the gradient computed before the sync.
+"""
+import math
+
+from common import batches_this_epoch, easgd_topology, forward_backward, setup, Throughput
+
+import torch
+
+import torch_distlearn_b200 as dl
+from torch_distlearn_b200.launch import shutdown
+from torch_distlearn_b200.models import cifar_convnet
+from torch_distlearn_b200.ops import local_sgd
+from torch_distlearn_b200.utils import Data
+from torch_distlearn_b200.utils.config import easgd_parser
+
+
+def main(argv=None):
+    opt = easgd_parser("EASGD client (examples/EASGD_client.lua)", "client").parse_args(argv)
+    world, server_rank, _ = easgd_topology(opt)
+    comm, log = setup(opt, rank=opt.nodeIndex, world=world)          # client i is rank i (the server is rank 0)
+    dev = comm.device
+    data = Data(opt.nodeIndex, opt.numNodes, opt.batchSize, device=dev, train_samples=opt.trainSamples,
+                test_samples=opt.testSamples)                        # partitioned over the clients (:75)
+    model = cifar_convnet(seed=opt.seed).to(dev)
+    flat = dl.FlatParams(comm, model)
+    algo = dl.AsyncEA(comm, "client", opt.communicationTime, opt.alpha, server_rank=server_rank,
+                      num_clients=opt.numNodes, exclusive=opt.exclusive, verbose=opt.verbose)
+    algo.initClient(flat, timeout=600.0)                             # :95 — start from the server's center
+    n_train = batches_this_epoch(data.numTrainingBatches(), opt)
+    for epoch in range(1, opt.numEpochs + 1):
+        thr, loss_sum, synced = Throughput(), 0.0, 0
+        for i in range(1, n_train + 1):
+            b = data.getTrainingBatch()
+            _, loss = forward_backward(model, b)                     # :106
+            synced += bool(algo.syncClient(flat))                    # :109
+            if dev.type == "cuda":                                   # :113-117
+                local_sgd(flat.params.tensor, flat.grads.tensor, None, lr=opt.learningRate, zero_grads=True)
+            else:
+                with torch.no_grad():
+                    flat.params.tensor.add_(flat.grads.tensor, alpha=-opt.learningRate)
+                flat.zero_grad()
+            thr.add(b.batchSize)
+            if i % 20 == 0 or i == n_train:
+                loss_sum = float(loss)
+        comm.synchronize()
+        print(f"[client {opt.nodeIndex}] epoch {epoch}: loss {loss_sum:.4f}  {synced} syncs  {thr.rate():.0f} samples/s", flush=True)
+    algo.finish()
+    comm.barrier()
+    shutdown(comm)
+
+
+if __name__ == "__main__":
+    main()

@@ -10,7 +10,7 @@ and write peer GPUs directly over NVLink 5 / NVSwitch.
     sgd.synchronizeParameters()
     loss.backward(); sgd.step(lr=0.1)               # ONE fused kernel: all-reduce + 1/n + SGD + all-gather
 """
-from .parallel.comm import (CommResult, Communicator, EmulatedCommunicator, HostCommunicator, P2PCommunicator,
+from .parallel.comm import (CommResult, Communicator, DistCommunicator, EmulatedCommunicator, HostCommunicator, P2PCommunicator,
                             SymBuffer, create_communicator)
 from .parallel.flat import FlatParams, TableStager, walk_table
 from .parallel.allreduce_sgd import AllReduceSGD
@@ -23,7 +23,7 @@ from .utils.color_print import print_client, print_server
 __version__ = "0.1.0"
 
 __all__ = [
-    "CommResult", "Communicator", "EmulatedCommunicator", "HostCommunicator", "P2PCommunicator", "SymBuffer",
+    "CommResult", "Communicator", "DistCommunicator", "EmulatedCommunicator", "HostCommunicator", "P2PCommunicator", "SymBuffer",
     "create_communicator", "FlatParams", "TableStager", "walk_table", "AllReduceSGD", "AllReduceEA", "AsyncEA",
     "LocalhostTree", "Tree", "save_checkpoint", "load_checkpoint", "print_client", "print_server",
 ]

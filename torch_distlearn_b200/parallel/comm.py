@@ -665,12 +665,160 @@ class EmulatedCommunicator(_CudaOps):
             self._c.rank = 0
 
 
+# =====================================================================================================
+# Across hosts / mixed CPU+GPU jobs: torch.distributed collectives
+# =====================================================================================================
+class DistCommunicator(Communicator):
+    """Same front end over ``torch.distributed`` — for jobs that do not fit one NVSwitch domain:
+    several hosts (examples/client_remote.lua:31-41, the ssh lines of examples/AsyncEASGD.sh:44-46) or
+    a mix of CPU and GPU nodes (examples/client_remote.sh:5-6).  The heap is a private tensor (offsets
+    still match across ranks, nothing is mapped remotely) and every operation is a library collective
+    (NCCL when every node is a GPU, gloo with host staging otherwise) followed by the local math — the
+    reference's dataflow, kept as the portability path.  One-sided AsyncEA needs peer-mapped memory and
+    is not available here."""
+
+    backend = "dist"
+
+    def __init__(self, rank: Optional[int] = None, world: Optional[int] = None, device: Optional[torch.device] = None,
+                 heap_mb: float = 256, group=None):
+        import torch.distributed as dist
+        if not dist.is_initialized():
+            raise RuntimeError("DistCommunicator needs an initialised torch.distributed process group")
+        self._dist, self._group = dist, group
+        world = dist.get_world_size(group) if world is None else world
+        rank = dist.get_rank(group) if rank is None else rank
+        device = device or torch.device("cpu")
+        heap_bytes = _round_up(int(heap_mb * (1 << 20)) + DL_PAD_BYTES, 4096)
+        super().__init__(rank, world, device, heap_bytes)
+        self._bytes = torch.zeros(heap_bytes, dtype=torch.uint8, device=device)
+        self._wire_cpu = dist.get_backend(group) != "nccl"       # gloo: CUDA tensors are staged through the host
+        self._last: Optional[CommResult] = None
+
+    def _local_bytes(self) -> torch.Tensor:
+        return self._bytes
+
+    # -- helpers ------------------------------------------------------------------------------------
+    def _wire(self, t: torch.Tensor) -> torch.Tensor:
+        return t.cpu() if (self._wire_cpu and t.is_cuda) else t
+
+    def _meet(self, active: int, payload: int, extra: float = 0.0):
+        """What the kernels' arrival barrier does: everybody learns everybody's (active, payload, extra)."""
+        mine = torch.tensor([float(active), float(payload), float(extra)], dtype=torch.float64,
+                            device="cpu" if self._wire_cpu else self.device)
+        out = [torch.empty_like(mine) for _ in range(self.world)]
+        self._dist.all_gather(out, mine, group=self._group)
+        rows = [o.tolist() for o in out]
+        flags = [int(r[0]) for r in rows]
+        n_active = sum(1 for a in flags if a & 1)
+        first = next((i for i, a in enumerate(flags) if a & 3), self.rank)
+        self._last = CommResult(n_active, [int(r[1]) for r in rows])
+        return flags, n_active, rows[first][2]
+
+    def _sum(self, t: torch.Tensor) -> None:
+        w = self._wire(t)
+        self._dist.all_reduce(w, group=self._group)
+        if w is not t:
+            t.copy_(w)
+
+    # -- collectives -----------------------------------------------------------------------------------
+    def barrier(self, active: int = 1, payload: int = 0, channel: int = 0, read: bool = True, stream=None):
+        self._meet(active, payload)
+        self.launches += 1
+        return self._last
+
+    def allreduce(self, buf: SymBuffer, n: Optional[int] = None, active: int = 1, payload: int = 0, normalize: bool = False,
+                  variant: str = "auto", channel: int = 0, read: bool = False, nblocks: int = 0, stream=None):
+        n = buf.numel if n is None else n
+        flags, n_active, norm = self._meet(active, payload, float(normalize))
+        t = buf.tensor[:n]
+        if not (active & 3):
+            t.zero_()                                   # a draining node contributes zeros (lua/AllReduceSGD.lua:37)
+        self._sum(t)
+        if norm and n_active > 1 and t.is_floating_point():
+            t.mul_(1.0 / n_active)
+        self.launches += 1
+        return self._last
+
+    def fused_sgd(self, grads: SymBuffer, params: SymBuffer, momentum_buf: Optional[SymBuffer], n: int, lr: float,
+                  momentum: float = 0.0, weight_decay: float = 0.0, nesterov: bool = False, active: int = 1,
+                  payload: int = 0, zero_grads: bool = True, variant: str = "auto", channel: int = 0, read: bool = False,
+                  nblocks: int = 0, stream=None):
+        flags, n_active, lr_used = self._meet(active, payload, lr)
+        g, p = grads.tensor[:n], params.tensor[:n]
+        if not (active & 3):
+            g.zero_()
+        self._sum(g)
+        if n_active > 0:
+            with torch.no_grad():
+                if n_active > 1:
+                    g.mul_(1.0 / n_active)
+                if weight_decay:
+                    g.add_(p, alpha=weight_decay)
+                if momentum_buf is not None:
+                    m = momentum_buf.tensor[:n]
+                    m.mul_(momentum).add_(g)
+                    g = g.add(m, alpha=momentum) if nesterov else m
+                p.add_(g, alpha=-float(lr_used))
+        if zero_grads:
+            grads.tensor[:n].zero_()
+        self.launches += 1
+        return self._last
+
+    def fused_ea(self, x: SymBuffer, c_cur: SymBuffer, c_next: SymBuffer, n: int, alpha: float, active: int = 1,
+                 payload: int = 0, variant: str = "auto", channel: int = 0, read: bool = False, nblocks: int = 0, stream=None):
+        flags, n_active, _ = self._meet(active, payload)
+        xv, c, cn = x.tensor[:n], c_cur.tensor[:n], c_next.tensor[:n]
+        if n_active > 0:                                # lua/AllReduceEA.lua:34-45, finished nodes still move (:58-68)
+            d = (xv - c) * alpha
+            xv.sub_(d)
+            self._sum(d)
+            torch.add(c, d, out=cn)
+        else:
+            cn.copy_(c)
+        self.launches += 1
+        return self._last
+
+    def broadcast(self, buf: SymBuffer, n: Optional[int] = None, root: int = 0, also: Optional[SymBuffer] = None,
+                  payload: int = 0, variant: str = "auto", channel: int = 0, read: bool = False, nblocks: int = 0, stream=None):
+        n = buf.numel if n is None else n
+        self._meet(1, payload)
+        t = buf.tensor[:n]
+        w = self._wire(t)
+        self._dist.broadcast(w, src=root if self._group is None else self._dist.get_global_rank(self._group, root), group=self._group)
+        if w is not t:
+            t.copy_(w)
+        if also is not None:
+            also.tensor[:n].copy_(t)
+        self.launches += 1
+        return self._last
+
+    def read_result(self, channel: int = 0, stream=None) -> CommResult:
+        return self._last if self._last is not None else CommResult(0, [0] * self.world)
+
+    def _no_async(self, *_a, **_k):
+        raise NotImplementedError("AsyncEA needs peer-mapped memory (P2PCommunicator / HostCommunicator); "
+                                  "the torch.distributed backend has no one-sided operations")
+
+    async_client_sync = peer_pull = sync_count = mailbox_write = mailbox_read = _no_async
+
+    def synchronize(self) -> None:
+        if self.device.type == "cuda":
+            torch.cuda.synchronize(self.device)
+
+    def describe(self) -> dict:
+        return {"backend": self.backend, "wire": "gloo+host staging" if self._wire_cpu else "nccl", "world": self.world,
+                "rank": self.rank, "heap_bytes": self.heap_bytes}
+
+
 def create_communicator(backend: str = "auto", **kw) -> Communicator:
-    """``backend``: 'p2p' (CUDA, default when a GPU is present), 'host' (CPU shared memory)."""
+    """``backend``: 'p2p' (CUDA, default when a GPU is present), 'host' (CPU shared memory),
+    'dist' (torch.distributed collectives: several hosts, mixed CPU/GPU nodes)."""
     if backend == "auto":
         backend = "p2p" if torch.cuda.is_available() else "host"
     if backend == "p2p":
         return P2PCommunicator(**kw)
     if backend == "host":
         return HostCommunicator(**kw)
+    if backend == "dist":
+        return DistCommunicator(**kw)
     raise ValueError(f"unknown backend {backend!r}")

@@ -33,8 +33,9 @@ def base_parser(description: str, batch_size: int = 32, learning_rate: float = 0
     p.add_argument("--weightDecay", type=float, default=0.0)
     p.add_argument("--variant", choices=["auto", "oneshot", "twoshot", "nvls"], default="auto",
                    help="collective algorithm (auto = measured variant table)")
-    p.add_argument("--backend", choices=["auto", "p2p", "host"], default="auto",
-                   help="p2p = CUDA symmetric heap over NVLink, host = CPU shared memory")
+    p.add_argument("--backend", choices=["auto", "p2p", "host", "dist"], default="auto",
+                   help="p2p = CUDA symmetric heap over NVLink, host = CPU shared memory, "
+                        "dist = torch.distributed collectives (several hosts, mixed CPU/GPU nodes)")
     p.add_argument("--heapMB", type=float, default=256.0, help="symmetric heap size per node")
     p.add_argument("--fused", action=argparse.BooleanOptionalAction, default=True,
                    help="use the fused all-reduce+SGD kernel (off = reference-style sumAndNormalizeGradients + local update)")
