@@ -1,0 +1,157 @@
+#!/usr/bin/env python
+"""asynchronous EASGD, CIFAR convnet, one center + (N-1) clients, tau=10, alpha=0.2.
+
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29562 \
+        bench/bench_async.py [--impl ours|hostloop] [--steps 200]
+
+ours     : rank 0 holds the center in its GPU's symmetric heap and does nothing per sync; every client
+           sync is ONE kernel on the client GPU (P2P loads of the center + red.add.v4.f32 of the elastic
+           difference over NVLink, csrc/async_ea.cu).
+hostloop : the reference's design (lua/AsyncEA.lua:230-237; examples/AsyncEASGD.sh:36 runs the server
+           without --cuda): a server process serialises the clients with recv-from-any, ships the center
+           and receives the delta through host memory (torch.distributed gloo; NCCL has no any-source recv).
+Clients run forward+backward+SGD of the CIFAR convnet at per-GPU batch 128 between syncs.  Reported:
+total client samples/s, syncs/s, mean time a client spends in one sync (device-timed in ours, wall in
+hostloop)."""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+import torch
+import torch.distributed as dist
+import torch.nn.functional as F
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--impl", choices=["ours", "hostloop"], default="ours")
+    ap.add_argument("--batch", type=int, default=128)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--tau", type=int, default=10)
+    ap.add_argument("--alpha", type=float, default=0.2)
+    ap.add_argument("--lr", type=float, default=0.01)
+    ap.add_argument("--exclusive", type=int, default=0)
+    args = ap.parse_args()
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    local = int(os.environ.get("LOCAL_RANK", rank))
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from torch_distlearn_b200.models import cifar_convnet
+    from torch_distlearn_b200.ops import local_sgd
+    model = cifar_convnet().to(dev)
+    B, clients = args.batch, world - 1
+    out = {}
+    if args.impl == "ours":
+        import torch_distlearn_b200 as dl
+        comm = dl.P2PCommunicator(rank=rank, world=world, device=dev, heap_mb=96)
+        flat = dl.FlatParams(comm, model)
+        algo = dl.AsyncEA(comm, "server" if rank == 0 else "client", args.tau, args.alpha, server_rank=0, num_clients=clients,
+                          exclusive=bool(args.exclusive))
+        if rank == 0:
+            algo.initServer(flat)
+            t0 = time.time()
+            while algo.syncServer(flat, timeout=None):
+                pass
+            out = {"syncs": algo.syncs, "server_wall_s": time.time() - t0}
+        else:
+            algo.initClient(flat, timeout=600.0)
+    else:
+        from baseline.nccl_algos import NcclFlat
+        flat = NcclFlat(model)
+        n = flat.params.numel()
+        if rank == 0:
+            center = flat.params.detach().cpu().clone()
+            delta = torch.zeros(n)
+            req = torch.zeros(1, dtype=torch.int64)
+            done, syncs, t0 = 0, 0, time.time()
+            while done < clients:
+                src = dist.recv(req)                      # recvAny = the mutex (lua/AsyncEA.lua:168)
+                if int(req[0]) < 0:
+                    done += 1
+                    continue
+                dist.send(center, dst=src)                # :185-190
+                dist.recv(delta, src=src)                 # :206-210
+                center.add_(delta)                        # :212-216
+                syncs += 1
+            out = {"syncs": syncs, "server_wall_s": time.time() - t0}
+        else:
+            host_x = torch.zeros(n).pin_memory()
+            host_c = torch.zeros(n).pin_memory()
+            req = torch.zeros(1, dtype=torch.int64)
+    if rank != 0:
+        g = torch.Generator().manual_seed(rank)
+        x = torch.randn(B, 3, 32, 32, generator=g).to(dev)
+        y = torch.randint(0, 10, (B,), generator=g).to(dev)
+        p = flat.params.tensor if args.impl == "ours" else flat.params
+        gr = flat.grads.tensor if args.impl == "ours" else flat.grads
+        sync_ms, n_sync = 0.0, 0
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+
+        def one_step(i, timed):
+            nonlocal sync_ms, n_sync
+            F.nll_loss(model(x), y).backward()
+            if (i + 1) % args.tau == 0:
+                if args.impl == "ours":
+                    if timed:
+                        ev0.record()
+                    algo.syncClient(flat)
+                    if timed:
+                        ev1.record()
+                        ev1.synchronize()
+                        sync_ms += ev0.elapsed_time(ev1)
+                        n_sync += 1
+                else:
+                    t = time.perf_counter()
+                    req[0] = rank
+                    dist.send(req, dst=0)                              # "Enter?"
+                    host_x.copy_(p, non_blocking=True)
+                    dist.recv(host_c, src=0)                           # center
+                    torch.cuda.current_stream().synchronize()
+                    d = (host_x - host_c) * args.alpha                 # lua/AsyncEA.lua:114
+                    dist.send(d, dst=0)                                # delta
+                    p.sub_(d.to(dev, non_blocking=True))               # :115
+                    if timed:
+                        sync_ms += (time.perf_counter() - t) * 1e3
+                        n_sync += 1
+            local_sgd(p, gr, None, lr=args.lr, zero_grads=True)
+
+        if args.impl == "ours":
+            algo.step = 0
+        for i in range(args.tau):
+            one_step(i, False)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for i in range(args.steps):
+            one_step(i, True)
+        torch.cuda.synchronize()
+        wall = time.perf_counter() - t0
+        if args.impl == "ours":
+            algo.finish()
+        else:
+            req[0] = -1
+            dist.send(req, dst=0)
+        out = {"samples_per_s": B * args.steps / wall, "sync_ms": sync_ms / max(n_sync, 1), "syncs": n_sync, "wall_s": wall}
+    res = [None] * world
+    dist.all_gather_object(res, out)
+    if rank == 0:
+        cl = res[1:]
+        print(json.dumps({"bench": "async_easgd_cifar", "impl": args.impl, "n_gpus": world, "clients": clients, "per_gpu_batch": B,
+                          "tau": args.tau, "alpha": args.alpha, "exclusive": bool(args.exclusive),
+                          "client_samples_per_s_total": round(sum(c["samples_per_s"] for c in cl), 1),
+                          "syncs_per_s": round(sum(c["syncs"] / c["wall_s"] for c in cl), 1),
+                          "mean_sync_ms": round(sum(c["sync_ms"] for c in cl) / len(cl), 4),
+                          "server_syncs_seen": res[0].get("syncs")}))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
