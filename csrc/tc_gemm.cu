@@ -1,0 +1,475 @@
+// tc_gemm — fp32-accurate GEMM on the 5th-generation tensor cores (tcgen05 + TMEM + TMA).
+//
+//     C[M,N] (+)= A[M,K] * B[N,K]^T (+ bias[N])        A, B, C row-major fp32, K contiguous in A and B
+//
+// The reference trains in strict fp32 (`grad.util.cast(params, 'float')`, examples/cifar10.lua:136) and
+// its convolutions are im2col + SGEMM (SpatialConvolutionMM, examples/Model.lua:20).  On B200 an fp32
+// FFMA GEMM tops out near 70 TFLOP/s while the tensor cores take TF32 inputs at >1 PFLOP/s, so this
+// kernel keeps fp32 accuracy with the 3xTF32 split:  a = a_hi + a_lo  (a_hi = a rounded to TF32,
+// a_lo = a - a_hi exactly),  a*b ~= a_hi*b_hi + a_hi*b_lo + a_lo*b_hi  accumulated in fp32 in TMEM
+// (the dropped a_lo*b_lo term is ~2^-22 relative).  `terms = 1` runs plain TF32 (a_hi*b_hi only).
+//
+// One CTA computes one 128 x BN output tile (optionally one K-split of it), warp-specialised:
+//   warp 0      TMA producer: cp.async.bulk.tensor 128x32 (A) and BNx32 (B) fp32 boxes, 128B swizzle,
+//               into a 3-stage ring, completion on mbarriers
+//   warps 2-5   converters: split the raw fp32 tile in place into hi (same buffer) and lo (sibling
+//               buffer) — element-wise at identical byte offsets, so the TMA swizzle is preserved —
+//               then fence.proxy.async and arrive; after the main loop the same warps are the epilogue
+//   warp 1      allocates TMEM; one elected lane issues tcgen05.mma.kind::tf32 (M=128, N=BN, K=8):
+//               3 products x 4 K-steps per stage; tcgen05.commit frees the stage / publishes the tile
+//   warps 6-9   accumulator drain + epilogue.  The tensor core adds into TMEM with truncation, which over
+//               thousands of K steps would cost ~1e-5 relative — more than an fp32 FFMA chain.  So the
+//               accumulator is double-buffered in TMEM and flushed every CHUNK K-blocks (K = 128):
+//               tcgen05.ld 32 lanes x 32 columns per warp, added into fp32 registers (round-to-nearest)
+//               while the MMAs of the next chunk run into the other buffer.  At the end: (+bias) ->
+//               128-byte row segments to global memory (st, or red.add for split-K / accumulate)
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <mutex>
+#include <unordered_map>
+
+#include "dl_host.h"
+
+namespace {
+
+constexpr int BM = 128;      // UMMA_M
+constexpr int BK = 32;       // fp32 elements per 128-byte swizzle row
+constexpr int UMMA_K = 8;    // K per tcgen05.mma.kind::tf32
+constexpr int STAGES = 3;
+constexpr int NUM_THREADS = 320;
+constexpr int CHUNK = 4;     // K-blocks accumulated inside TMEM before the fp32 register flush
+
+struct GemmArgs {
+  float* C;
+  const float* bias;
+  int M, N, K;
+  long long ldc;
+  int kblocks_per_split;  // K blocks (of BK) each blockIdx.z handles
+  int atomic_out;         // 1: red.add into C (split-K or accumulate), 0: plain store
+  int terms;              // 3 = 3xTF32 (fp32-accurate), 1 = TF32
+  int a_mn, b_mn;         // operand stored with its M / N dimension contiguous ([K, MN] row-major) instead of K
+  int vec_out;            // rows of C are 16-byte aligned: float4 stores / red.v4
+};
+
+// ---- PTX wrappers ------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return static_cast<uint32_t>(__cvta_generic_to_shared(p)); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+// Bounded wait: a mis-programmed pipeline must fail the launch, not hang the GPU.
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  for (uint32_t i = 0; i < (1u << 26); ++i)
+    if (mbar_try_wait(bar, parity)) return;
+  __trap();
+}
+__device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(
+          smem_u32(dst)),
+      "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
+      "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ float tf32_round(float x) {
+  uint32_t r;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+  return __uint_as_float(r);
+}
+
+// K-major operand tile with 128-byte swizzle: rows of 128 bytes, 8-row groups 1024 bytes apart.
+__device__ __forceinline__ uint64_t make_desc(uint32_t smem_addr) {
+  uint64_t d = 0;
+  d |= static_cast<uint64_t>((smem_addr & 0x3FFFFu) >> 4);  // start address, 16-byte units
+  d |= static_cast<uint64_t>(1) << 16;                       // leading byte offset (unused with swizzle)
+  d |= static_cast<uint64_t>(1024 >> 4) << 32;               // stride byte offset: next 8-row group
+  d |= static_cast<uint64_t>(1) << 46;                       // descriptor version (Blackwell)
+  d |= static_cast<uint64_t>(2) << 61;                       // SWIZZLE_128B
+  return d;
+}
+
+// MN-major operand tile, as TMA writes it from a [K, MN] row-major matrix in boxes of 32 K-rows x 32 MN-elements.
+// For 32-bit (TF32) operands the tensor core accepts exactly one MN-major shared-memory layout: 128-byte rows
+// swizzled in 32-byte chunks (UMMA layout type 1 = SWIZZLE_128B_BASE32B, TMA CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B),
+// whose atom is 4 K-rows x 128 bytes.  Inside a box the 4-row atoms are 512 bytes apart (SBO); boxes (the next
+// 32 MN elements) are 4096 bytes apart (LBO).  One tcgen05.mma (K = 8) consumes two atoms = 1024 bytes.
+__device__ __forceinline__ uint64_t make_desc_mn(uint32_t smem_addr) {
+  uint64_t d = 0;
+  d |= static_cast<uint64_t>((smem_addr & 0x3FFFFu) >> 4);
+  d |= static_cast<uint64_t>(4096 >> 4) << 16;               // leading byte offset: next 32 MN elements
+  d |= static_cast<uint64_t>(512 >> 4) << 32;                // stride byte offset: next 4 K rows
+  d |= static_cast<uint64_t>(1) << 46;
+  d |= static_cast<uint64_t>(1) << 61;                       // SWIZZLE_128B_BASE32B
+  return d;
+}
+
+template <int BN>
+struct Smem {
+  // [stage][0 = hi (TMA destination), 1 = lo]; every tile is 1024-byte aligned (swizzle atom)
+  float a[STAGES][2][BM * BK];
+  float b[STAGES][2][BN * BK];
+  uint64_t full[STAGES], conv[STAGES], empty[STAGES], acc_full[2], acc_empty[2];
+  uint32_t tmem_base;
+};
+
+template <int BN>
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+tc_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, GemmArgs g) {
+  extern __shared__ __align__(1024) unsigned char smem_raw[];
+  Smem<BN>& s = *reinterpret_cast<Smem<BN>*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int m0 = blockIdx.x * BM, n0 = blockIdx.y * BN;
+  const int total_kb = (g.K + BK - 1) / BK;
+  const int kb_begin = blockIdx.z * g.kblocks_per_split;
+  int kb_end = kb_begin + g.kblocks_per_split;
+  if (kb_end > total_kb) kb_end = total_kb;
+  const int nkb = kb_end - kb_begin;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < STAGES; ++i) {
+      mbar_init(&s.full[i], 1);
+      mbar_init(&s.conv[i], 128);
+      mbar_init(&s.empty[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&s.acc_full[i], 1);
+      mbar_init(&s.acc_empty[i], 128);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {  // TMEM: two accumulator buffers of BN fp32 columns each (a power of two >= 32 in total)
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s.tmem_base)), "n"(2 * BN) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem = s.tmem_base;
+
+  if (nkb > 0) {
+    if (warp == 0) {
+      // ===== TMA producer =====
+      if (lane == 0) {
+        for (int i = 0; i < nkb; ++i) {
+          const int st = i % STAGES, it = i / STAGES;
+          mbar_wait(&s.empty[st], (it & 1) ^ 1);
+          mbar_expect_tx(&s.full[st], (BM + BN) * BK * 4);
+          const int k0 = (kb_begin + i) * BK;
+          if (!g.a_mn) {
+            tma_load_2d(&s.a[st][0][0], &map_a, &s.full[st], k0, m0);
+          } else {
+            for (int bx = 0; bx < BM / 32; ++bx) tma_load_2d(&s.a[st][0][bx * 32 * BK], &map_a, &s.full[st], m0 + 32 * bx, k0);
+          }
+          if (!g.b_mn) {
+            tma_load_2d(&s.b[st][0][0], &map_b, &s.full[st], k0, n0);
+          } else {
+            for (int bx = 0; bx < BN / 32; ++bx) tma_load_2d(&s.b[st][0][bx * 32 * BK], &map_b, &s.full[st], n0 + 32 * bx, k0);
+          }
+        }
+      }
+    } else if (warp == 1) {
+      // ===== MMA issuer =====
+      // instruction descriptor: D = fp32, A = B = TF32, both K-major, N = BN, M = 128
+      const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | (static_cast<uint32_t>(BN >> 3) << 17) |
+                             (static_cast<uint32_t>(BM >> 4) << 24) | (g.a_mn ? (1u << 15) : 0u) | (g.b_mn ? (1u << 16) : 0u);
+      for (int i = 0; i < nkb; ++i) {
+        const int st = i % STAGES, it = i / STAGES;
+        const int chunk = i / CHUNK, buf = chunk & 1, use = chunk >> 1;
+        const bool first_in_chunk = (i % CHUNK) == 0, last_in_chunk = (i % CHUNK) == CHUNK - 1 || i == nkb - 1;
+        if (first_in_chunk) mbar_wait(&s.acc_empty[buf], (use & 1) ^ 1);   // drain warps are done with this buffer
+        mbar_wait(&s.conv[st], it & 1);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        if (lane == 0) {
+          const uint32_t acc = tmem + static_cast<uint32_t>(buf * BN);
+          const uint32_t pa_hi = smem_u32(&s.a[st][0][0]), pa_lo = smem_u32(&s.a[st][1][0]);
+          const uint32_t pb_hi = smem_u32(&s.b[st][0][0]), pb_lo = smem_u32(&s.b[st][1][0]);
+          const uint64_t a_hi = g.a_mn ? make_desc_mn(pa_hi) : make_desc(pa_hi), a_lo = g.a_mn ? make_desc_mn(pa_lo) : make_desc(pa_lo);
+          const uint64_t b_hi = g.b_mn ? make_desc_mn(pb_hi) : make_desc(pb_hi), b_lo = g.b_mn ? make_desc_mn(pb_lo) : make_desc(pb_lo);
+          // one K step (8 elements): K-major = 32 bytes along the swizzled row, MN-major = the next 8-row group (1024 bytes)
+          const uint64_t a_step = g.a_mn ? (1024 >> 4) : ((UMMA_K * 4) >> 4), b_step = g.b_mn ? (1024 >> 4) : ((UMMA_K * 4) >> 4);
+#pragma unroll
+          for (int k = 0; k < BK / UMMA_K; ++k) {
+            const uint64_t aa = a_step * k, bb = b_step * k;
+            const uint32_t keep = (first_in_chunk && k == 0) ? 0u : 1u;          // a new chunk overwrites its buffer
+            if (g.terms == 3) {
+              // small terms first, the dominant product last
+              umma_tf32(acc, a_lo + aa, b_hi + bb, idesc, keep);
+              umma_tf32(acc, a_hi + aa, b_lo + bb, idesc, 1u);
+              umma_tf32(acc, a_hi + aa, b_hi + bb, idesc, 1u);
+            } else {
+              umma_tf32(acc, a_hi + aa, b_hi + bb, idesc, keep);
+            }
+          }
+          umma_commit(&s.empty[st]);                          // stage reusable once these MMAs have read it
+          if (last_in_chunk) umma_commit(&s.acc_full[buf]);   // chunk complete: hand the buffer to the drain warps
+        }
+        __syncwarp();
+      }
+    } else if (warp < 6) {
+      // ===== converters (warps 2..5, 128 threads) =====
+      const int t = threadIdx.x - 64;
+      for (int i = 0; i < nkb; ++i) {
+        const int st = i % STAGES, it = i / STAGES;
+        mbar_wait(&s.full[st], it & 1);
+        float4* a_hi = reinterpret_cast<float4*>(&s.a[st][0][0]);
+        float4* a_lo = reinterpret_cast<float4*>(&s.a[st][1][0]);
+        float4* b_hi = reinterpret_cast<float4*>(&s.b[st][0][0]);
+        float4* b_lo = reinterpret_cast<float4*>(&s.b[st][1][0]);
+        const bool three = g.terms == 3;
+#pragma unroll 4
+        for (int j = t; j < BM * BK / 4; j += 128) {
+          const float4 v = a_hi[j];
+          const float4 h = make_float4(tf32_round(v.x), tf32_round(v.y), tf32_round(v.z), tf32_round(v.w));
+          a_hi[j] = h;
+          if (three) a_lo[j] = make_float4(v.x - h.x, v.y - h.y, v.z - h.z, v.w - h.w);
+        }
+#pragma unroll 4
+        for (int j = t; j < BN * BK / 4; j += 128) {
+          const float4 v = b_hi[j];
+          const float4 h = make_float4(tf32_round(v.x), tf32_round(v.y), tf32_round(v.z), tf32_round(v.w));
+          b_hi[j] = h;
+          if (three) b_lo[j] = make_float4(v.x - h.x, v.y - h.y, v.z - h.z, v.w - h.w);
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy writes -> visible to the tensor core
+        mbar_arrive(&s.conv[st]);
+      }
+    } else {
+      // ===== drain + epilogue (warps 6..9): this warp owns TMEM lanes [32*(warp%4), +32) = output rows =====
+      const int quarter = warp & 3;
+      const int row = m0 + quarter * 32 + lane;
+      float acc[BN];
+#pragma unroll
+      for (int j = 0; j < BN; ++j) acc[j] = 0.f;
+      const int nchunks = (nkb + CHUNK - 1) / CHUNK;
+      for (int c = 0; c < nchunks; ++c) {
+        const int buf = c & 1, use = c >> 1;
+        mbar_wait(&s.acc_full[buf], use & 1);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+#pragma unroll
+        for (int c0 = 0; c0 < BN; c0 += 32) {
+          uint32_t r[32];
+          const uint32_t taddr = tmem + (static_cast<uint32_t>(quarter * 32) << 16) + static_cast<uint32_t>(buf * BN + c0);
+          asm volatile(
+              "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+              "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+              "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+              : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+                "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+                "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+                "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+              : "r"(taddr)
+              : "memory");
+          asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+          for (int q = 0; q < 32; ++q) acc[c0 + q] += __uint_as_float(r[q]);
+        }
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+        mbar_arrive(&s.acc_empty[buf]);                      // the MMA warp may overwrite this buffer
+      }
+      if (row < g.M) {
+        float* crow = g.C + static_cast<long long>(row) * g.ldc + n0;
+        const bool add_bias = g.bias != nullptr && blockIdx.z == 0;
+#pragma unroll
+        for (int q = 0; q < BN; q += 4) {
+          const int n = n0 + q;
+          if (n + 3 < g.N && g.vec_out) {
+            float4 v = make_float4(acc[q], acc[q + 1], acc[q + 2], acc[q + 3]);
+            if (add_bias) {
+              const float4 bv = *reinterpret_cast<const float4*>(g.bias + n);
+              v.x += bv.x; v.y += bv.y; v.z += bv.z; v.w += bv.w;
+            }
+            if (g.atomic_out) {
+              asm volatile("red.relaxed.gpu.global.add.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(crow + q), "f"(v.x), "f"(v.y),
+                           "f"(v.z), "f"(v.w)
+                           : "memory");
+            } else {
+              *reinterpret_cast<float4*>(crow + q) = v;
+            }
+          } else {
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              if (n + e < g.N) {
+                float v = acc[q + e];
+                if (add_bias) v += g.bias[n + e];
+                if (g.atomic_out) atomicAdd(crow + q + e, v);
+                else crow[q + e] = v;
+              }
+            }
+          }
+        }
+      }
+    }
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if (warp == 1) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(2 * BN) : "memory");
+  }
+}
+
+// ---- host: tensor maps ----------------------------------------------------------------------------
+typedef CUresult (*EncodeTiled_t)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiled_t encode_fn() {
+  static EncodeTiled_t fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiled_t>(p);
+  });
+  return fn;
+}
+
+int ensure_context() {
+  typedef CUresult (*GetCurrent_t)(CUcontext*);
+  typedef CUresult (*SetCurrent_t)(CUcontext);
+  typedef CUresult (*Retain_t)(CUcontext*, CUdevice);
+  static GetCurrent_t get_cur = nullptr;
+  static SetCurrent_t set_cur = nullptr;
+  static Retain_t retain = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuCtxGetCurrent", &p, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
+      get_cur = reinterpret_cast<GetCurrent_t>(p);
+    if (cudaGetDriverEntryPoint("cuCtxSetCurrent", &p, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
+      set_cur = reinterpret_cast<SetCurrent_t>(p);
+    if (cudaGetDriverEntryPoint("cuDevicePrimaryCtxRetain", &p, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
+      retain = reinterpret_cast<Retain_t>(p);
+  });
+  DL_REQUIRE(get_cur && set_cur && retain, "tc_gemm: driver context entry points are not available");
+  thread_local bool bound = false;
+  if (bound) return DL_OK;
+  CUcontext ctx = nullptr;
+  if (get_cur(&ctx) == CUDA_SUCCESS && ctx != nullptr) {
+    bound = true;
+    return DL_OK;
+  }
+  int dev = 0;
+  DL_CUDA(cudaGetDevice(&dev));
+  DL_REQUIRE(retain(&ctx, dev) == CUDA_SUCCESS && ctx != nullptr, "tc_gemm: cannot retain the primary context of device %d", dev);
+  DL_REQUIRE(set_cur(ctx) == CUDA_SUCCESS, "tc_gemm: cannot bind the primary context of device %d to this thread", dev);
+  bound = true;
+  return DL_OK;
+}
+
+// 2-D fp32 row-major matrix [rows, cols] with row pitch ld (elements); box = box_rows x 32 columns, 128B swizzle
+int make_map(CUtensorMap* map, const float* ptr, long long rows, long long cols, long long ld, int box_rows, bool mn_major) {
+  DL_REQUIRE(reinterpret_cast<uintptr_t>(ptr) % 16 == 0 && ld % 4 == 0, "tc_gemm: operands must be 16-byte aligned with a row pitch that is a multiple of 4 floats");
+  EncodeTiled_t enc = encode_fn();
+  DL_REQUIRE(enc != nullptr, "tc_gemm: cuTensorMapEncodeTiled is not available from this driver");
+  cuuint64_t dims[2] = {static_cast<cuuint64_t>(cols), static_cast<cuuint64_t>(rows)};
+  cuuint64_t strides[1] = {static_cast<cuuint64_t>(ld) * 4};
+  cuuint32_t box[2] = {static_cast<cuuint32_t>(BK), static_cast<cuuint32_t>(box_rows)};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(ptr), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, mn_major ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  DL_REQUIRE(r == CUDA_SUCCESS, "tc_gemm: cuTensorMapEncodeTiled failed with CUresult %d (ptr %p rows %lld cols %lld ld %lld)",
+             static_cast<int>(r), static_cast<const void*>(ptr), rows, cols, ld);
+  return DL_OK;
+}
+
+template <int BN>
+int launch(const CUtensorMap& ma, const CUtensorMap& mb, const GemmArgs& g, int splits, cudaStream_t st) {
+  static bool configured[64] = {false};
+  int dev = 0;
+  DL_CUDA(cudaGetDevice(&dev));
+  const size_t smem = sizeof(Smem<BN>) + 1024;
+  if (dev >= 0 && dev < 64 && !configured[dev]) {
+    DL_CUDA(cudaFuncSetAttribute(tc_gemm_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+    configured[dev] = true;
+  }
+  dim3 grid((g.M + BM - 1) / BM, (g.N + BN - 1) / BN, splits);
+  tc_gemm_kernel<BN><<<grid, NUM_THREADS, smem, st>>>(ma, mb, g);
+  DL_CUDA(cudaGetLastError());
+  return DL_OK;
+}
+
+}  // namespace
+
+extern "C" int dl_tc_gemm_ex(const float* A, const float* B, float* C, const float* bias, int M, int N, int K, long long lda,
+                             long long ldb, long long ldc, int a_mn, int b_mn, int split_k, int accumulate, int terms,
+                             void* stream) {
+  DL_REQUIRE(A && B && C, "dl_tc_gemm: null pointer");
+  DL_REQUIRE(M > 0 && N > 0 && K > 0, "dl_tc_gemm: empty problem %d x %d x %d", M, N, K);
+  DL_REQUIRE(terms == 1 || terms == 3, "dl_tc_gemm: terms must be 1 (TF32) or 3 (3xTF32, fp32-accurate)");
+  DL_REQUIRE(reinterpret_cast<uintptr_t>(C) % 4 == 0, "dl_tc_gemm: C must be 4-byte aligned");
+  const int total_kb = (K + BK - 1) / BK;
+  if (split_k < 1) split_k = 1;
+  if (split_k > total_kb) split_k = total_kb;
+  GemmArgs g;
+  g.C = C; g.bias = bias; g.M = M; g.N = N; g.K = K; g.ldc = ldc;
+  g.kblocks_per_split = (total_kb + split_k - 1) / split_k;
+  const int splits = (total_kb + g.kblocks_per_split - 1) / g.kblocks_per_split;
+  g.atomic_out = (splits > 1 || accumulate) ? 1 : 0;
+  g.terms = terms;
+  g.a_mn = a_mn ? 1 : 0;
+  g.b_mn = b_mn ? 1 : 0;
+  g.vec_out = (reinterpret_cast<uintptr_t>(C) % 16 == 0 && ldc % 4 == 0 &&
+               (bias == nullptr || reinterpret_cast<uintptr_t>(bias) % 16 == 0)) ? 1 : 0;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int bn = N <= 64 ? 64 : 128;
+  // The tensor-map encoder is a raw driver entry point: it needs a context current on THIS thread (autograd
+  // runs backward on worker threads that may only have used the runtime API lazily).  Binding the primary
+  // context through the driver API is legal during stream capture, unlike cudaFree(0).
+  {
+    const int rc_ctx = ensure_context();
+    if (rc_ctx != DL_OK) return rc_ctx;
+  }
+  CUtensorMap ma, mb;
+  // K-major: [MN rows, K cols], box = (tile rows) x 32 K;  MN-major: [K rows, MN cols], box = 32 K rows x 32 MN
+  int rc = a_mn ? make_map(&ma, A, K, M, lda, BK, true) : make_map(&ma, A, M, K, lda, BM, false);
+  if (rc != DL_OK) return rc;
+  rc = b_mn ? make_map(&mb, B, K, N, ldb, BK, true) : make_map(&mb, B, N, K, ldb, bn, false);
+  if (rc != DL_OK) return rc;
+  if (splits > 1 && !accumulate) {
+    // split-K partial sums are added with atomics: start from zero (row by row: C may be a strided view)
+    if (ldc == N) {
+      DL_CUDA(cudaMemsetAsync(C, 0, static_cast<size_t>(M) * N * 4, st));
+    } else {
+      DL_CUDA(cudaMemset2DAsync(C, static_cast<size_t>(ldc) * 4, 0, static_cast<size_t>(N) * 4, M, st));
+    }
+  }
+  return bn == 64 ? launch<64>(ma, mb, g, splits, st) : launch<128>(ma, mb, g, splits, st);
+}
+
+extern "C" int dl_tc_gemm(const float* A, const float* B, float* C, const float* bias, int M, int N, int K, long long lda,
+                          long long ldb, long long ldc, int split_k, int accumulate, int terms, void* stream) {
+  return dl_tc_gemm_ex(A, B, C, bias, M, N, K, lda, ldb, ldc, 0, 0, split_k, accumulate, terms, stream);
+}

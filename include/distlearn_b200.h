@@ -158,6 +158,28 @@ int dl_async_sync_count(const dl_comm_t* c, int server, uint64_t* count, void* s
 int dl_mailbox_write(const dl_comm_t* c, int rank, int index, uint64_t value, void* stream);
 int dl_mailbox_read(const dl_comm_t* c, int rank, int index, uint64_t* value, void* stream);
 
+/* ---- tensor-core GEMM (tcgen05 + TMEM + TMA), fp32 in / fp32 out ---- */
+/* C[M,N] (+)= A[M,K] * B[N,K]^T (+ bias[N]); A, B, C row-major fp32 with K contiguous in A and B
+ * (leading dimensions in elements, multiples of 4).  terms = 3: 3xTF32 split with fp32-level accuracy
+ * (the reference is strict fp32, examples/cifar10.lua:136; its convolutions are im2col + SGEMM,
+ * examples/Model.lua:20); terms = 1: plain TF32.  split_k > 1 splits K over blockIdx.z and adds the
+ * partial tiles with red.add (C is zeroed first unless accumulate != 0, which adds into C as is). */
+int dl_tc_gemm(const float* A, const float* B, float* C, const float* bias, int M, int N, int K, long long lda,
+               long long ldb, long long ldc, int split_k, int accumulate, int terms, void* stream);
+/* Same, with either operand optionally "MN-major": a_mn != 0 means A is stored as [K, M] row-major
+ * (M contiguous), b_mn != 0 means B is stored as [K, N] row-major.  This is what the weight-gradient
+ * GEMM  dW[Cout, Kc] = dY[M, Cout]^T * col[M, Kc]  and the data-gradient GEMM  dcol = dY * W  need,
+ * without materialising any transpose. */
+int dl_tc_gemm_ex(const float* A, const float* B, float* C, const float* bias, int M, int N, int K, long long lda,
+                  long long ldb, long long ldc, int a_mn, int b_mn, int split_k, int accumulate, int terms,
+                  void* stream);
+
+/* 5x5 / stride 1 / pad 2 convolution pieces on NHWC activations (SpatialConvolutionMM = im2col + GEMM,
+ * examples/Model.lua:20-38): col[B*H*W, ld] with columns ordered (kh, kw, cin); col2im sums the 25 taps
+ * back into dx[B,H,W,C]. */
+int dl_im2col5x5(const float* x, float* col, int B, int H, int W, int C, long long ld, void* stream);
+int dl_col2im5x5(const float* dcol, float* dx, int B, int H, int W, int C, long long ld, void* stream);
+
 /* ---- local flat-vector ops (single GPU, no communication) ---- */
 /* p -= lr * (g*scale [+ wd*p] [momentum]); optionally zero g. world==1 fast path. */
 int dl_local_sgd(float* p, float* g, float* m, uint64_t n, float lr, float momentum,

@@ -105,6 +105,10 @@ def cuda():
     _sig(lib, "dl_async_sync_count", i32, [cp, i32, P(u64), vp])
     _sig(lib, "dl_mailbox_write", i32, [cp, i32, i32, u64, vp])
     _sig(lib, "dl_mailbox_read", i32, [cp, i32, i32, P(u64), vp])
+    _sig(lib, "dl_tc_gemm", i32, [vp, vp, vp, vp, i32, i32, i32, C.c_longlong, C.c_longlong, C.c_longlong, i32, i32, i32, vp])
+    _sig(lib, "dl_tc_gemm_ex", i32, [vp, vp, vp, vp, i32, i32, i32, C.c_longlong, C.c_longlong, C.c_longlong, i32, i32, i32, i32, i32, vp])
+    _sig(lib, "dl_im2col5x5", i32, [vp, vp, i32, i32, i32, i32, C.c_longlong, vp])
+    _sig(lib, "dl_col2im5x5", i32, [vp, vp, i32, i32, i32, i32, C.c_longlong, vp])
     _sig(lib, "dl_local_sgd", i32, [vp, vp, vp, u64, f32, f32, f32, i32, f32, i32, vp])
     _sig(lib, "dl_local_ea", i32, [vp, vp, u64, f32, vp])
     _sig(lib, "dl_sumsq_scratch_bytes", sz, [])

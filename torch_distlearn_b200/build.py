@@ -33,6 +33,8 @@ CUDA_SOURCES = [
     "broadcast.cu",
     "async_ea.cu",
     "local_ops.cu",
+    "tc_gemm.cu",
+    "conv_ops.cu",
 ]
 HOST_SOURCES = ["host_transport.cpp"]
 

@@ -31,6 +31,44 @@ class CifarConvNet(nn.Module):
         return F.log_softmax(x, dim=1)                             # :64
 
 
+class CifarConvNetTC(nn.Module):
+    """The same network with every convolution on the tensor cores (ops/conv.py: im2col + the tcgen05
+    3xTF32 GEMM of csrc/tc_gemm.cu, fp32-level accuracy) and NHWC activations.  Same parameter count
+    (4,328,970); conv weights are stored as GEMM operands [cout, 25*cin], the Linear layer sees the
+    features in the reference's (c, h, w) order, so ``load_reference`` maps parameters one to one."""
+    CHANNELS = CifarConvNet.CHANNELS
+
+    def __init__(self, terms: int = 3):
+        super().__init__()
+        from ..ops.conv import TCConv5x5
+        self.convs = nn.ModuleList([TCConv5x5(cin, cout, terms) for cin, cout in zip(self.CHANNELS[:-1], self.CHANNELS[1:])])
+        self.bns = nn.ModuleList([nn.BatchNorm2d(c, eps=1e-3) for c in self.CHANNELS[1:]])
+        self.linear = nn.Linear(512 * 2 * 2, 10)
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        x = x.permute(0, 2, 3, 1).contiguous()                     # NCHW input batch -> NHWC once
+        for conv, bn in zip(self.convs, self.bns):
+            y = conv(x).permute(0, 3, 1, 2)                        # NHWC data seen as a channels_last NCHW tensor
+            y = F.max_pool2d(F.relu(bn(y)), 2, 2)                  # cuDNN / ATen channels_last kernels
+            x = y.permute(0, 2, 3, 1)                              # contiguous NHWC again (no copy)
+        x = self.linear(x.permute(0, 3, 1, 2).reshape(x.shape[0], 2048))   # (c, h, w) feature order, examples/Model.lua:44
+        return F.log_softmax(x, dim=1)
+
+    @torch.no_grad()
+    def load_reference(self, ref: CifarConvNet) -> "CifarConvNetTC":
+        for mine, theirs in zip(self.convs, ref.convs):
+            mine.load_conv2d(theirs)
+        for mine, theirs in zip(self.bns, ref.bns):
+            mine.load_state_dict(theirs.state_dict())
+        self.linear.load_state_dict(ref.linear.state_dict())
+        return self
+
+
+def cifar_convnet_tc(seed: int = 0, terms: int = 3) -> CifarConvNetTC:
+    """Same initial weights as ``cifar_convnet(seed)`` (built from it), convolutions on tcgen05."""
+    return CifarConvNetTC(terms).load_reference(cifar_convnet(seed))
+
+
 def cifar_convnet(seed: int = 0) -> CifarConvNet:
     """``torch.manualSeed(0)`` on every node before construction (examples/Model.lua:17)."""
     gen_state = torch.random.get_rng_state()

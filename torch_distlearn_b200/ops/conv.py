@@ -1,0 +1,127 @@
+"""5x5 / stride 1 / pad 2 convolution on the Blackwell tensor cores, forward and backward.
+
+The reference's convolution is ``SpatialConvolutionMM`` (examples/Model.lua:20,26,32,38): im2col + SGEMM
+in strict fp32.  Same decomposition here, NHWC activations, with the three GEMMs of a training step on
+tcgen05 (csrc/tc_gemm.cu, 3xTF32 = fp32-level accuracy):
+
+    forward   y[M, Cout]      = col[M, 25 Cin] @ W[Cout, 25 Cin]^T + bias          (K-major x K-major)
+    wgrad     dW[Cout, 25Cin] = dY[M, Cout]^T @ col[M, 25 Cin]                     (MN-major x MN-major, split-K over M)
+    dgrad     dcol[M, 25 Cin] = dY[M, Cout] @ W[Cout, 25 Cin]  ->  col2im -> dX    (K-major x MN-major)
+
+with M = B*H*W and the (kh, kw, cin) column order of ``col``; no operand is ever transposed in memory.
+"""
+from __future__ import annotations
+
+import math
+from typing import Optional
+
+import torch
+
+from .. import _lib
+from .tc_gemm import tc_gemm
+
+TAPS = 25
+
+
+def _stream(t: torch.Tensor) -> int:
+    return torch.cuda.current_stream(t.device).cuda_stream
+
+
+def im2col5x5(x: torch.Tensor, ld: Optional[int] = None, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """x [B,H,W,C] (contiguous NHWC) -> col [B*H*W, ld], ld = 25*C rounded up to a multiple of 4."""
+    assert x.is_cuda and x.dtype == torch.float32 and x.is_contiguous() and x.dim() == 4
+    B, H, W, C = x.shape
+    ld = ld or (TAPS * C + 3) // 4 * 4
+    if out is None:
+        out = torch.empty(B * H * W, ld, dtype=torch.float32, device=x.device)
+    with torch.cuda.device(x.device):
+        _lib.check(_lib.cuda().dl_im2col5x5(x.data_ptr(), out.data_ptr(), B, H, W, C, ld, _stream(x)))
+    return out
+
+
+def col2im5x5(dcol: torch.Tensor, shape) -> torch.Tensor:
+    """dcol [B*H*W, ld] -> dx [B,H,W,C]."""
+    B, H, W, C = shape
+    assert dcol.is_cuda and dcol.is_contiguous() and dcol.shape[0] == B * H * W
+    dx = torch.empty(B, H, W, C, dtype=torch.float32, device=dcol.device)
+    with torch.cuda.device(dcol.device):
+        _lib.check(_lib.cuda().dl_col2im5x5(dcol.data_ptr(), dx.data_ptr(), B, H, W, C, dcol.shape[1], _stream(dcol)))
+    return dx
+
+
+def _splits(m_tiles: int, n_tiles: int, k: int, sms: int = 148) -> int:
+    """Split K so that roughly two waves of CTAs exist, keeping >= 128 K (4 K-blocks) per split."""
+    tiles = max(m_tiles * n_tiles, 1)
+    want = max(1, (2 * sms + tiles - 1) // tiles)
+    return max(1, min(want, k // 128))
+
+
+class _Conv5x5(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, weight, bias, terms):
+        x = x.contiguous()
+        B, H, W, C = x.shape
+        cout, kc = weight.shape
+        assert kc == TAPS * C, f"weight must be [Cout, 25*Cin] = [{cout}, {TAPS * C}]"
+        col = im2col5x5(x)
+        ld = col.shape[1]
+        w = weight
+        if ld != kc:                                    # Cin = 3: pad K to a multiple of 4 with zero columns
+            w = torch.zeros(cout, ld, dtype=weight.dtype, device=weight.device)
+            w[:, :kc] = weight
+        M = B * H * W
+        bn = 64 if cout <= 64 else 128
+        y = tc_gemm(col, w, bias=bias, split_k=_splits((M + 127) // 128, (cout + bn - 1) // bn, ld), terms=terms)
+        ctx.save_for_backward(col, w)
+        ctx.meta = (B, H, W, C, cout, kc, terms, bias is not None)
+        return y.view(B, H, W, cout)
+
+    @staticmethod
+    def backward(ctx, dy):
+        col, w = ctx.saved_tensors
+        B, H, W, C, cout, kc, terms, has_bias = ctx.meta
+        M, ld = col.shape
+        dy2 = dy.contiguous().view(M, cout)
+        dx = dw = db = None
+        if ctx.needs_input_grad[1]:
+            bn = 64 if ld <= 64 else 128
+            dw_full = tc_gemm(dy2, col, a_mn=True, b_mn=True, terms=terms,
+                              split_k=_splits((cout + 127) // 128, (ld + bn - 1) // bn, M))
+            dw = dw_full[:, :kc] if ld != kc else dw_full
+        if has_bias and ctx.needs_input_grad[2]:
+            db = dy2.sum(0)
+        if ctx.needs_input_grad[0]:
+            dcol = tc_gemm(dy2, w, b_mn=True, terms=terms)          # [M, ld]; K = Cout is short, no split
+            dx = col2im5x5(dcol, (B, H, W, C))
+        return dx, dw, db, None
+
+
+def conv5x5_nhwc(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor] = None, terms: int = 3) -> torch.Tensor:
+    """x [B,H,W,Cin] NHWC, weight [Cout, 25*Cin] with columns ordered (kh, kw, cin) -> y [B,H,W,Cout]."""
+    return _Conv5x5.apply(x, weight, bias, terms)
+
+
+class TCConv5x5(torch.nn.Module):
+    """``nn.Conv2d(cin, cout, 5, 1, 2)`` with NHWC activations and the weight kept as the GEMM operand
+    ``[cout, 25*cin]`` ((kh, kw, cin) column order).  Same initialisation distribution as nn.Conv2d."""
+
+    def __init__(self, cin: int, cout: int, terms: int = 3):
+        super().__init__()
+        self.cin, self.cout, self.terms = cin, cout, terms
+        self.weight = torch.nn.Parameter(torch.empty(cout, TAPS * cin))
+        self.bias = torch.nn.Parameter(torch.empty(cout))
+        bound = 1.0 / math.sqrt(cin * TAPS)
+        torch.nn.init.uniform_(self.weight, -bound, bound)       # kaiming_uniform(a=sqrt(5)) == U(-1/sqrt(fan_in), +)
+        torch.nn.init.uniform_(self.bias, -bound, bound)
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        return conv5x5_nhwc(x, self.weight, self.bias, self.terms)
+
+    @torch.no_grad()
+    def load_conv2d(self, conv: torch.nn.Conv2d) -> None:
+        """Copy the weights of an ``nn.Conv2d`` ([cout, cin, 5, 5] -> [cout, (kh, kw, cin)])."""
+        self.weight.copy_(conv.weight.permute(0, 2, 3, 1).reshape(self.cout, -1))
+        self.bias.copy_(conv.bias)
+
+    def extra_repr(self) -> str:
+        return f"{self.cin}, {self.cout}, kernel_size=5, padding=2, layout=NHWC, gemm=tcgen05 {'3xTF32' if self.terms == 3 else 'TF32'}"
