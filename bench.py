@@ -38,6 +38,10 @@ def parse():
     p.add_argument("--variant", default="auto")
     p.add_argument("--nblocks", type=int, default=0)
     p.add_argument("--heap-mb", type=float, default=128)
+    p.add_argument("--conv", choices=["tc", "cudnn"], default="tc",
+                   help="ours: tc = convolutions as implicit GEMMs on tcgen05 (3xTF32, fp32-level accuracy, csrc/tc_gemm.cu); "
+                        "cudnn = stock torch modules (what the nccl baseline always uses)")
+    p.add_argument("--conv-terms", type=int, default=3, choices=[1, 3], help="3 = 3xTF32 (fp32-accurate), 1 = plain TF32")
     p.add_argument("--bucket-mb", type=float, default=0.0,
                    help="ours: launch the fused kernel per gradient bucket of this size, overlapped with backward (0 = one launch)")
     p.add_argument("--bucket-blocks", type=int, default=32, help="CTAs per bucket launch (leaves the other SMs to cuDNN)")
@@ -82,11 +86,14 @@ def main() -> None:
         else:
             dist.init_process_group("gloo", rank=rank, world_size=world)  # bootstrap only
 
-    from torch_distlearn_b200.models import cifar_convnet
+    from torch_distlearn_b200.models import cifar_convnet, cifar_convnet_tc
     from torch_distlearn_b200.utils.timing import ClockSampler, max_over_ranks
 
     B = args.per_gpu_batch
-    model = cifar_convnet().to(dev)
+    use_tc = args.impl == "ours" and args.conv == "tc"
+    model = (cifar_convnet_tc(terms=args.conv_terms) if use_tc else cifar_convnet()).to(dev)
+    conv_desc = (f"tcgen05 implicit GEMM, {'3xTF32 (fp32-level accuracy)' if args.conv_terms == 3 else 'TF32'}" if use_tc
+                 else f"cuDNN via torch, allow_tf32={bool(args.tf32)}")
     K, W = args.steps, max(args.warmup, 3)
     # a pool of distinct pinned host batches, cycled: every step copies a fresh batch
     pool = 8
@@ -187,7 +194,7 @@ def main() -> None:
     barrier()
     sampler = ClockSampler(gpu_index=local_rank, period_ms=100).start() if rank == 0 else None
     if args.impl == "ours":
-        l0 = comm.launches
+        l0 = step.kernel_launches
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     e0.record()
@@ -197,7 +204,7 @@ def main() -> None:
     barrier()
     ms = e0.elapsed_time(e1)
     if args.impl == "ours":
-        launches = comm.launches - l0
+        launches = step.kernel_launches - l0      # every kernel of libdistlearn_b200 in the timed region (graph replays included)
     ms = max_over_ranks(ms, world)
     # ---- end-to-end region (public API, H2D + D2H every step) -------------------------------------
     for i in range(3):
@@ -232,7 +239,7 @@ def main() -> None:
             "data": "synthetic CIFAR-shaped 3x32x32, random-init weights", "impl": args.impl,
             "config": {"model": "cifar10_convnet (examples/Model.lua, 4,328,970 params)", "global_batch": total,
                        "per_gpu_batch": B, "seq_len": None, "parallelism": f"dp{world}", "lr": args.lr,
-                       "tf32": bool(args.tf32), "cuda_graph": bool(args.graph), "bucket_mb": args.bucket_mb,
+                       "tf32": bool(args.tf32), "conv": conv_desc, "cuda_graph": bool(args.graph), "bucket_mb": args.bucket_mb,
                        "l2": "no explicit flush: each step streams >126 MB of activations/gradients (working set > L2)",
                        "transport": describe},
             "e2e": {"value": round(e2e_value, 1), "unit": "samples/s", "h2d_bytes_per_step": h2d_bytes,

@@ -143,6 +143,7 @@ extern "C" int dl_async_ea_client(const dl_comm_t* c, int server, float* x, uint
   AsyncArgs a;
   a.x = x; a.c_off = c_off; a.n = n; a.alpha = alpha; a.server = server; a.exclusive = exclusive;
   async_ea_client_kernel<<<nb, DL_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(*c, a);
+  dl_note_launch();
   DL_CUDA(cudaGetLastError());
   return DL_OK;
 }

@@ -164,6 +164,7 @@ extern "C" int dl_peer_pull(const dl_comm_t* c, int src_rank, uint64_t off, floa
   const int tail = static_cast<int>(n - n4 * 4);
   peer_pull_kernel<<<nb, DL_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(
       reinterpret_cast<const float4*>(src), reinterpret_cast<float4*>(dst), n4, src + n4 * 4, dst + n4 * 4, tail);
+  dl_note_launch();
   DL_CUDA(cudaGetLastError());
   return DL_OK;
 }

@@ -92,6 +92,7 @@ extern "C" int dl_im2col5x5(const float* x, float* col, int B, int H, int W, int
   const long long items = static_cast<long long>(B) * H * W * (vec ? ld / 4 : ld);
   if (vec) im2col5x5_kernel<4><<<conv_grid(items), 256, 0, st>>>(x, col, B, H, W, C, ld);
   else im2col5x5_kernel<1><<<conv_grid(items), 256, 0, st>>>(x, col, B, H, W, C, ld);
+  dl_note_launch();
   DL_CUDA(cudaGetLastError());
   return DL_OK;
 }
@@ -104,6 +105,7 @@ extern "C" int dl_col2im5x5(const float* dcol, float* dx, int B, int H, int W, i
   const long long items = static_cast<long long>(B) * H * W * (vec ? C / 4 : C);
   if (vec) col2im5x5_kernel<4><<<conv_grid(items), 256, 0, st>>>(dcol, dx, B, H, W, C, ld);
   else col2im5x5_kernel<1><<<conv_grid(items), 256, 0, st>>>(dcol, dx, B, H, W, C, ld);
+  dl_note_launch();
   DL_CUDA(cudaGetLastError());
   return DL_OK;
 }

@@ -14,6 +14,11 @@ void dl_set_error(const char* fmt, ...) {
 }
 
 extern "C" const char* dl_last_error(void) { return g_err; }
+
+#include <atomic>
+static std::atomic<unsigned long long> g_launches{0};
+void dl_note_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
+extern "C" unsigned long long dl_kernel_launches(void) { return g_launches.load(std::memory_order_relaxed); }
 extern "C" int dl_version(void) { return 100; }
 
 int dl_sm_count() {

@@ -7,6 +7,8 @@
 #include "../include/distlearn_b200.h"
 
 void dl_set_error(const char* fmt, ...);
+// Every kernel launch of the library is counted (host side) so that callers can report how many of OUR kernels ran.
+void dl_note_launch();
 
 #define DL_CUDA(expr)                                                                      \
   do {                                                                                     \
@@ -44,5 +46,6 @@ int dl_launch(void (*kernel)(Args...), const dl_comm_t* c, int nblocks, int thre
     kernel<<<grid, threads, 0, stream>>>(args...);
     DL_CUDA(cudaGetLastError());
   }
+  dl_note_launch();
   return DL_OK;
 }

@@ -175,6 +175,7 @@ extern "C" int dl_local_ea(float* x, float* c, uint64_t n, float alpha, void* st
   DL_REQUIRE(x && c, "dl_local_ea: null pointer");
   if (n == 0) return DL_OK;
   local_ea_kernel<<<dl_pick_blocks(n, 4, 0), DL_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(x, c, n, alpha);
+  dl_note_launch();
   DL_CUDA(cudaGetLastError());
   return DL_OK;
 }

@@ -304,6 +304,7 @@ extern "C" int dl_local_sgd(float* p, float* g, float* m, uint64_t n, float lr, 
   a.scale = grad_scale; a.nesterov = nesterov; a.zero_grads = zero_grads;
   const int nb = dl_pick_blocks(n / 4 + 1, 2, 0);
   local_sgd_kernel<<<nb, DL_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(a);
+  dl_note_launch();
   DL_CUDA(cudaGetLastError());
   return DL_OK;
 }

@@ -59,6 +59,7 @@ extern "C" int dl_sumsq_diff(const float* a, const float* b, uint64_t n, double*
   DL_REQUIRE(reinterpret_cast<uintptr_t>(scratch) % 8 == 0, "dl_sumsq_diff: scratch must be 8-byte aligned");
   sumsq_diff_kernel<<<sumsq_blocks(n), DL_SUMSQ_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(
       a, b, n, out, static_cast<SumsqScratch*>(scratch));
+  dl_note_launch();
   DL_CUDA(cudaGetLastError());
   return DL_OK;
 }
@@ -85,6 +86,7 @@ extern "C" int dl_confusion_add(const float* logits, const int64_t* target, int 
   if (batch == 0) return DL_OK;
   confusion_add_kernel<<<(batch + 127) / 128, 128, 0, static_cast<cudaStream_t>(stream)>>>(
       logits, reinterpret_cast<const long long*>(target), batch, classes, reinterpret_cast<unsigned long long*>(mat));
+  dl_note_launch();
   DL_CUDA(cudaGetLastError());
   return DL_OK;
 }
@@ -147,6 +149,7 @@ extern "C" int dl_sumsq_diff_static(const float* a, const float* b, uint64_t n, 
   SumsqScratch* s = static_cast<SumsqScratch*>(scratch);
   DL_CUDA(cudaMemsetAsync(&s->arrived, 0, sizeof(s->arrived), st));
   sumsq_diff_kernel<<<nb, DL_SUMSQ_THREADS, 0, st>>>(a, b, n, out, s);
+  dl_note_launch();
   DL_CUDA(cudaGetLastError());
   return DL_OK;
 }

@@ -51,6 +51,16 @@ struct GemmArgs {
   int terms;              // 3 = 3xTF32 (fp32-accurate), 1 = TF32
   int a_mn, b_mn;         // operand stored with its M / N dimension contiguous ([K, MN] row-major) instead of K
   int vec_out;            // rows of C are 16-byte aligned: float4 stores / red.v4
+  // implicit-GEMM convolution (5x5, stride 1, pad 2, NHWC): the operand marked (*) is read straight from the
+  // activation tensor with 4-D TMA boxes shifted by the filter tap — out-of-image elements arrive as zeros,
+  // so no im2col / col2im buffer exists.
+  //   mode 1 forward : C[pixels, Cout] = sum_{tap,c}  X(*)[pixel + tap, c]   * W[cout, (tap, c)]
+  //   mode 2 dgrad   : C[pixels, Cin]  = sum_{tap,co} dY(*)[pixel - tap, co] * W[co, (tap, cin)]   (W read MN-major)
+  //   mode 3 wgrad   : C[Cout, 25 Cin] = sum_pixels   dY[pixel, cout]        * X(*)[pixel + tap, c]  (both MN-major)
+  int mode;
+  int cH, cW;             // image height / width
+  int cA;                 // channels of the 4-D tensor on the A side (mode 1: Cin, mode 2: Cout)
+  int cIn;                // Cin (modes 2 and 3)
 };
 
 // ---- PTX wrappers ------------------------------------------------------------------------------
@@ -87,6 +97,13 @@ __device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, u
       "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(
           smem_u32(dst)),
       "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_4d(void* dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1, int c2, int c3) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];" ::"r"(
+          smem_u32(dst)),
+      "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
       : "memory");
 }
 __device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
@@ -183,16 +200,46 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
           const int st = i % STAGES, it = i / STAGES;
           mbar_wait(&s.empty[st], (it & 1) ^ 1);
           mbar_expect_tx(&s.full[st], (BM + BN) * BK * 4);
-          const int k0 = (kb_begin + i) * BK;
-          if (!g.a_mn) {
-            tma_load_2d(&s.a[st][0][0], &map_a, &s.full[st], k0, m0);
-          } else {
+          const int kb = kb_begin + i;
+          const int k0 = kb * BK;
+          if (g.mode == 1 || g.mode == 2) {
+            // A tile = 128 consecutive pixels of the NHWC tensor, shifted by the filter tap of this K block
+            const int hw = g.cH * g.cW;
+            const int b0 = m0 / hw, h0 = (m0 - b0 * hw) / g.cW;
+            const int per_tap = g.cA / BK;
+            const int tap = kb / per_tap, cb = kb - tap * per_tap;
+            int dh = tap / 5 - 2, dw = tap % 5 - 2;
+            if (g.mode == 2) { dh = -dh; dw = -dw; }
+            tma_load_4d(&s.a[st][0][0], &map_a, &s.full[st], cb * BK, dw, h0 + dh, b0);
+            if (g.mode == 1) {
+              tma_load_2d(&s.b[st][0][0], &map_b, &s.full[st], k0, n0);
+            } else {
+              // W[co, (tap, cin)] as an MN-major operand: rows = this block of 32 output channels, columns = tap*Cin + n
+              for (int bx = 0; bx < BN / 32; ++bx)
+                tma_load_2d(&s.b[st][0][bx * 32 * BK], &map_b, &s.full[st], tap * g.cIn + n0 + 32 * bx, cb * BK);
+            }
+          } else if (g.mode == 3) {
             for (int bx = 0; bx < BM / 32; ++bx) tma_load_2d(&s.a[st][0][bx * 32 * BK], &map_a, &s.full[st], m0 + 32 * bx, k0);
-          }
-          if (!g.b_mn) {
-            tma_load_2d(&s.b[st][0][0], &map_b, &s.full[st], k0, n0);
+            // B boxes = 32 consecutive pixels (the K block) x 32 channels of one tap, straight from X
+            const int hw = g.cH * g.cW;
+            const int b0 = k0 / hw, h0 = (k0 - b0 * hw) / g.cW;
+            for (int bx = 0; bx < BN / 32; ++bx) {
+              const int col = n0 + 32 * bx;
+              const int tap = col / g.cIn, c0 = col - tap * g.cIn;
+              if (tap < 25) tma_load_4d(&s.b[st][0][bx * 32 * BK], &map_b, &s.full[st], c0, tap % 5 - 2, h0 + tap / 5 - 2, b0);
+              else tma_load_4d(&s.b[st][0][bx * 32 * BK], &map_b, &s.full[st], g.cIn, 0, 0, 0);   // past the last tap: zeros
+            }
           } else {
-            for (int bx = 0; bx < BN / 32; ++bx) tma_load_2d(&s.b[st][0][bx * 32 * BK], &map_b, &s.full[st], n0 + 32 * bx, k0);
+            if (!g.a_mn) {
+              tma_load_2d(&s.a[st][0][0], &map_a, &s.full[st], k0, m0);
+            } else {
+              for (int bx = 0; bx < BM / 32; ++bx) tma_load_2d(&s.a[st][0][bx * 32 * BK], &map_a, &s.full[st], m0 + 32 * bx, k0);
+            }
+            if (!g.b_mn) {
+              tma_load_2d(&s.b[st][0][0], &map_b, &s.full[st], k0, n0);
+            } else {
+              for (int bx = 0; bx < BN / 32; ++bx) tma_load_2d(&s.b[st][0][bx * 32 * BK], &map_b, &s.full[st], n0 + 32 * bx, k0);
+            }
           }
         }
       }
@@ -405,6 +452,30 @@ int make_map(CUtensorMap* map, const float* ptr, long long rows, long long cols,
   return DL_OK;
 }
 
+// 4-D map over an NHWC fp32 tensor [B, H, W, C]: box = 32 channels x (pixels) pixels laid out as whole image rows
+// (and whole images when an image has fewer pixels than the box).  Out-of-range coordinates, negative ones
+// included, read as zeros: that is the convolution's padding.
+int make_map_nhwc(CUtensorMap* map, const float* ptr, int B, int H, int W, int C, int pixels, bool mn_major) {
+  EncodeTiled_t enc = encode_fn();
+  DL_REQUIRE(enc != nullptr, "tc_conv: cuTensorMapEncodeTiled is not available from this driver");
+  DL_REQUIRE(reinterpret_cast<uintptr_t>(ptr) % 16 == 0 && C % 4 == 0, "tc_conv: NHWC tensors must be 16-byte aligned with C %% 4 == 0");
+  DL_REQUIRE(pixels % W == 0, "tc_conv: image width %d must divide the %d-pixel box", W, pixels);
+  const int rows = pixels / W;
+  const int bh = rows < H ? rows : H;
+  DL_REQUIRE(H % bh == 0 && rows % bh == 0, "tc_conv: a %d-pixel box does not tile %dx%d images", pixels, H, W);
+  const int bb = rows / bh;
+  cuuint64_t dims[4] = {static_cast<cuuint64_t>(C), static_cast<cuuint64_t>(W), static_cast<cuuint64_t>(H), static_cast<cuuint64_t>(B)};
+  cuuint64_t strides[3] = {static_cast<cuuint64_t>(C) * 4, static_cast<cuuint64_t>(W) * C * 4, static_cast<cuuint64_t>(H) * W * C * 4};
+  cuuint32_t box[4] = {static_cast<cuuint32_t>(BK), static_cast<cuuint32_t>(W), static_cast<cuuint32_t>(bh), static_cast<cuuint32_t>(bb)};
+  cuuint32_t estr[4] = {1, 1, 1, 1};
+  CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, const_cast<float*>(ptr), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, mn_major ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  DL_REQUIRE(r == CUDA_SUCCESS, "tc_conv: cuTensorMapEncodeTiled (NHWC %dx%dx%dx%d, box %d px) failed with CUresult %d", B, H, W, C,
+             pixels, static_cast<int>(r));
+  return DL_OK;
+}
+
 template <int BN>
 int launch(const CUtensorMap& ma, const CUtensorMap& mb, const GemmArgs& g, int splits, cudaStream_t st) {
   static bool configured[64] = {false};
@@ -417,6 +488,7 @@ int launch(const CUtensorMap& ma, const CUtensorMap& mb, const GemmArgs& g, int 
   }
   dim3 grid((g.M + BM - 1) / BM, (g.N + BN - 1) / BN, splits);
   tc_gemm_kernel<BN><<<grid, NUM_THREADS, smem, st>>>(ma, mb, g);
+  dl_note_launch();
   DL_CUDA(cudaGetLastError());
   return DL_OK;
 }
@@ -441,6 +513,7 @@ extern "C" int dl_tc_gemm_ex(const float* A, const float* B, float* C, const flo
   g.terms = terms;
   g.a_mn = a_mn ? 1 : 0;
   g.b_mn = b_mn ? 1 : 0;
+  g.mode = 0; g.cH = g.cW = g.cA = g.cIn = 0;
   g.vec_out = (reinterpret_cast<uintptr_t>(C) % 16 == 0 && ldc % 4 == 0 &&
                (bias == nullptr || reinterpret_cast<uintptr_t>(bias) % 16 == 0)) ? 1 : 0;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
@@ -472,4 +545,59 @@ extern "C" int dl_tc_gemm_ex(const float* A, const float* B, float* C, const flo
 extern "C" int dl_tc_gemm(const float* A, const float* B, float* C, const float* bias, int M, int N, int K, long long lda,
                           long long ldb, long long ldc, int split_k, int accumulate, int terms, void* stream) {
   return dl_tc_gemm_ex(A, B, C, bias, M, N, K, lda, ldb, ldc, 0, 0, split_k, accumulate, terms, stream);
+}
+
+// Implicit-GEMM 5x5 / stride 1 / pad 2 convolution pieces on NHWC tensors (see GemmArgs::mode).
+//   mode 1: act = x  [B,H,W,Cin],  w = W[Cout, 25*Cin], out = y  [B*H*W, Cout] (+ bias)
+//   mode 2: act = dy [B,H,W,Cout], w = W,               out = dx [B*H*W, Cin]
+//   mode 3: act = x  [B,H,W,Cin],  w = dy [B*H*W, Cout] (the other operand), out = dW [Cout, 25*Cin]
+extern "C" int dl_tc_conv5x5(int mode, const float* act, const float* w, float* out, const float* bias, int B, int H, int W,
+                             int Cin, int Cout, int split_k, int accumulate, int terms, void* stream) {
+  DL_REQUIRE(mode >= 1 && mode <= 3, "dl_tc_conv5x5: mode must be 1 (forward), 2 (dgrad) or 3 (wgrad)");
+  DL_REQUIRE(act && w && out && B > 0 && H > 0 && W > 0, "dl_tc_conv5x5: bad arguments");
+  DL_REQUIRE(Cin % BK == 0 && Cout % BK == 0, "dl_tc_conv5x5: Cin (%d) and Cout (%d) must be multiples of %d", Cin, Cout, BK);
+  DL_REQUIRE(terms == 1 || terms == 3, "dl_tc_conv5x5: terms must be 1 or 3");
+  const long long pixels = static_cast<long long>(B) * H * W;
+  const int kc = 25 * Cin;
+  {
+    const int rc_ctx = ensure_context();
+    if (rc_ctx != DL_OK) return rc_ctx;
+  }
+  GemmArgs g;
+  g.C = out; g.bias = mode == 1 ? bias : nullptr; g.terms = terms;
+  g.mode = mode; g.cH = H; g.cW = W; g.cIn = Cin;
+  g.a_mn = mode == 3; g.b_mn = mode != 1;
+  CUtensorMap ma, mb;
+  int rc;
+  if (mode == 1) {
+    g.M = static_cast<int>(pixels); g.N = Cout; g.K = kc; g.cA = Cin;
+    rc = make_map_nhwc(&ma, act, B, H, W, Cin, BM, false);
+    if (rc != DL_OK) return rc;
+  } else if (mode == 2) {
+    g.M = static_cast<int>(pixels); g.N = Cin; g.K = 25 * Cout; g.cA = Cout;
+    rc = make_map_nhwc(&ma, act, B, H, W, Cout, BM, false);
+    if (rc != DL_OK) return rc;
+  } else {
+    g.M = Cout; g.N = kc; g.K = static_cast<int>(pixels); g.cA = 0;
+    DL_REQUIRE(pixels % BK == 0, "dl_tc_conv5x5: wgrad needs B*H*W (%lld) to be a multiple of %d", pixels, BK);
+    rc = make_map(&ma, w, pixels, Cout, Cout, BK, true);                 // dY [pixels, Cout] as MN-major A
+    if (rc != DL_OK) return rc;
+  }
+  const int bn = g.N <= 64 ? 64 : 128;
+  if (mode == 1) rc = make_map(&mb, w, Cout, kc, kc, bn, false);         // W K-major
+  else if (mode == 2) rc = make_map(&mb, w, Cout, kc, kc, BK, true);     // W MN-major: rows = cout (K), cols = (tap, cin)
+  else rc = make_map_nhwc(&mb, act, B, H, W, Cin, BK, true);             // X as MN-major B, 32-pixel boxes
+  if (rc != DL_OK) return rc;
+  g.ldc = g.N;
+  const int total_kb = (g.K + BK - 1) / BK;
+  if (split_k < 1) split_k = 1;
+  if (split_k > total_kb) split_k = total_kb;
+  g.kblocks_per_split = (total_kb + split_k - 1) / split_k;
+  const int splits = (total_kb + g.kblocks_per_split - 1) / g.kblocks_per_split;
+  g.atomic_out = (splits > 1 || accumulate) ? 1 : 0;
+  g.vec_out = (reinterpret_cast<uintptr_t>(out) % 16 == 0 && g.ldc % 4 == 0 &&
+               (g.bias == nullptr || reinterpret_cast<uintptr_t>(g.bias) % 16 == 0)) ? 1 : 0;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (splits > 1 && !accumulate) DL_CUDA(cudaMemsetAsync(out, 0, static_cast<size_t>(g.M) * g.N * 4, st));
+  return bn == 64 ? launch<64>(ma, mb, g, splits, st) : launch<128>(ma, mb, g, splits, st);
 }

@@ -67,6 +67,8 @@ typedef struct dl_result {
 
 const char* dl_last_error(void);
 int dl_version(void);
+/* Number of kernels this library has launched so far in this process (host-side count). */
+unsigned long long dl_kernel_launches(void);
 
 /* ---- symmetric heap: CUDA VMM + POSIX-fd export (+ multicast), cudaIpc fallback ---- */
 /* Replaces libipc's socket transport + CUDA-IPC hint (examples/mnist.lua:93). */
@@ -173,6 +175,16 @@ int dl_tc_gemm(const float* A, const float* B, float* C, const float* bias, int 
 int dl_tc_gemm_ex(const float* A, const float* B, float* C, const float* bias, int M, int N, int K, long long lda,
                   long long ldb, long long ldc, int a_mn, int b_mn, int split_k, int accumulate, int terms,
                   void* stream);
+
+/* Implicit-GEMM 5x5 / stride 1 / pad 2 convolution on NHWC fp32 tensors (Cin, Cout multiples of 32): the
+ * tcgen05 GEMM above with its TMA producer reading the activation tensor in 4-D boxes shifted by the filter
+ * tap (zero fill = padding), so no im2col / col2im buffer exists.  Replaces SpatialConvolutionMM forward and
+ * both of its backward passes (examples/Model.lua:26,32,38).
+ *   mode 1 forward: act = x [B,H,W,Cin],  w = W [Cout, 25*Cin] ((kh,kw,cin) columns), out = y [B*H*W, Cout] (+bias)
+ *   mode 2 dgrad  : act = dy [B,H,W,Cout], w = W,                                      out = dx [B*H*W, Cin]
+ *   mode 3 wgrad  : act = x [B,H,W,Cin],  w = dy [B*H*W, Cout],                        out = dW [Cout, 25*Cin] */
+int dl_tc_conv5x5(int mode, const float* act, const float* w, float* out, const float* bias, int B, int H, int W,
+                  int Cin, int Cout, int split_k, int accumulate, int terms, void* stream);
 
 /* 5x5 / stride 1 / pad 2 convolution pieces on NHWC activations (SpatialConvolutionMM = im2col + GEMM,
  * examples/Model.lua:20-38): col[B*H*W, ld] with columns ordered (kh, kw, cin); col2im sums the 25 taps

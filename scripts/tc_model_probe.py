@@ -69,3 +69,19 @@ for (cin, cout, H) in [(3, 64, 32), (64, 128, 16), (128, 256, 8), (256, 512, 4)]
     t_dg = t(lambda: tc_gemm(dy, w, b_mn=True, out=dcol))
     t_c2i = t(lambda: col2im5x5(dcol, (B, H, H, cin)))
     print(f"conv {cin}->{cout} @{H}x{H}: im2col {t_i2c:.0f}us  fwd {t_fwd:.0f}us  wgrad {t_wg:.0f}us  dgrad {t_dg:.0f}us  col2im {t_c2i:.0f}us", flush=True)
+
+# implicit-GEMM pieces (no im2col / col2im)
+from torch_distlearn_b200.ops.conv import _tc_conv, _implicit_ok, TAPS
+for (cin, cout, H) in [(64, 128, 16), (128, 256, 8), (256, 512, 4)]:
+    if not _implicit_ok(B, H, H, cin, cout):
+        continue
+    xh = torch.randn(B, H, H, cin, device=dev); M = B * H * H
+    w = torch.randn(cout, 25 * cin, device=dev); dy = torch.randn(B, H, H, cout, device=dev)
+    y = torch.empty(M, cout, device=dev); dw = torch.empty(cout, 25 * cin, device=dev); dx = torch.empty(B, H, H, cin, device=dev)
+    bn = 64 if cout <= 64 else 128
+    bnc = 64 if cin <= 64 else 128
+    t_f = t(lambda: _tc_conv(1, xh, w, y, None, B, H, H, cin, cout, _splits((M + 127) // 128, (cout + bn - 1) // bn, TAPS * cin), 3))
+    t_w = t(lambda: _tc_conv(3, xh, dy, dw, None, B, H, H, cin, cout, _splits((cout + 127) // 128, (25 * cin + 127) // 128, M), 3))
+    t_d = t(lambda: _tc_conv(2, dy, w, dx, None, B, H, H, cin, cout, _splits((M + 127) // 128, (cin + bnc - 1) // bnc, TAPS * cout), 3))
+    fl = 2.0 * M * cout * 25 * cin
+    print(f"implicit conv {cin}->{cout} @{H}x{H}: fwd {t_f:.0f}us ({fl / t_f / 1e6:.0f}TF)  wgrad {t_w:.0f}us ({fl / t_w / 1e6:.0f}TF)  dgrad {t_d:.0f}us ({fl / t_d / 1e6:.0f}TF)", flush=True)

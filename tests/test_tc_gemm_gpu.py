@@ -89,11 +89,16 @@ def _conv_case(B, cin, cout, H, seed=0):
     return x, conv, dy
 
 
-@pytest.mark.parametrize("B,cin,cout,H", [(4, 3, 64, 32), (8, 64, 128, 16), (6, 128, 256, 8), (4, 256, 512, 4)])
-def test_conv5x5_forward_backward_vs_float64_conv2d(B, cin, cout, H):
+@pytest.mark.parametrize("implicit", [False, True])
+@pytest.mark.parametrize("B,cin,cout,H", [(4, 3, 64, 32), (8, 64, 128, 16), (6, 128, 256, 8), (4, 256, 512, 4), (128, 64, 128, 16)])
+def test_conv5x5_forward_backward_vs_float64_conv2d(B, cin, cout, H, implicit):
+    """Explicit (im2col + GEMM + col2im) and implicit (4-D TMA halo boxes) paths against float64 conv2d."""
     from torch_distlearn_b200.ops import TCConv5x5
+    from torch_distlearn_b200.ops.conv import _implicit_ok
+    if implicit and not _implicit_ok(B, H, H, cin, cout):
+        pytest.skip("geometry handled by the explicit path")
     x, conv, dy = _conv_case(B, cin, cout, H)
-    tc = TCConv5x5(cin, cout).to(DEV)
+    tc = TCConv5x5(cin, cout, implicit=implicit).to(DEV)
     tc.load_conv2d(conv)
     x_nhwc = x.permute(0, 2, 3, 1).contiguous().requires_grad_(True)
     y = tc(x_nhwc)

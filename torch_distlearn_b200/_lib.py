@@ -69,6 +69,7 @@ def cuda():
     cp = P(DlComm)
     _sig(lib, "dl_last_error", C.c_char_p, [])
     _sig(lib, "dl_version", i32, [])
+    _sig(lib, "dl_kernel_launches", u64, [])
     _sig(lib, "dl_device_caps", i32, [i32, P(i32), P(i32), P(i32)])
     _sig(lib, "dl_vmm_granularity", i32, [i32, P(sz)])
     _sig(lib, "dl_vmm_alloc", i32, [i32, sz, P(u64), P(i32)])
@@ -107,6 +108,7 @@ def cuda():
     _sig(lib, "dl_mailbox_read", i32, [cp, i32, i32, P(u64), vp])
     _sig(lib, "dl_tc_gemm", i32, [vp, vp, vp, vp, i32, i32, i32, C.c_longlong, C.c_longlong, C.c_longlong, i32, i32, i32, vp])
     _sig(lib, "dl_tc_gemm_ex", i32, [vp, vp, vp, vp, i32, i32, i32, C.c_longlong, C.c_longlong, C.c_longlong, i32, i32, i32, i32, i32, vp])
+    _sig(lib, "dl_tc_conv5x5", i32, [i32, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, vp])
     _sig(lib, "dl_im2col5x5", i32, [vp, vp, i32, i32, i32, i32, C.c_longlong, vp])
     _sig(lib, "dl_col2im5x5", i32, [vp, vp, i32, i32, i32, i32, C.c_longlong, vp])
     _sig(lib, "dl_local_sgd", i32, [vp, vp, vp, u64, f32, f32, f32, i32, f32, i32, vp])

@@ -9,6 +9,11 @@ tcgen05 (csrc/tc_gemm.cu, 3xTF32 = fp32-level accuracy):
     dgrad     dcol[M, 25 Cin] = dY[M, Cout] @ W[Cout, 25 Cin]  ->  col2im -> dX    (K-major x MN-major)
 
 with M = B*H*W and the (kh, kw, cin) column order of ``col``; no operand is ever transposed in memory.
+
+When Cin and Cout are multiples of 32 (every layer of the CIFAR net but the first) even ``col`` does not
+exist: the GEMM's TMA producer reads the activation tensor itself with 4-D boxes shifted by the filter
+tap, out-of-image elements arriving as zeros (``dl_tc_conv5x5``: implicit GEMM for forward, dgrad and
+wgrad).  The explicit im2col / col2im path remains for Cin = 3.
 """
 from __future__ import annotations
 
@@ -56,6 +61,63 @@ def _splits(m_tiles: int, n_tiles: int, k: int, sms: int = 148) -> int:
     return max(1, min(want, k // 128))
 
 
+def _implicit_ok(B: int, H: int, W: int, cin: int, cout: int) -> bool:
+    """Geometry the 4-D TMA boxes support: whole image rows tile the 128- and 32-pixel boxes."""
+    if cin % 32 or cout % 32 or W > 32 or 32 % W or 128 % W:
+        return False
+    for px in (128, 32):
+        rows = px // W
+        bh = min(rows, H)
+        if H % bh or rows % bh:
+            return False
+    return (B * H * W) % 32 == 0
+
+
+def _tc_conv(mode: int, act: torch.Tensor, w: torch.Tensor, out: torch.Tensor, bias, B, H, W, cin, cout, split_k, terms) -> torch.Tensor:
+    with torch.cuda.device(act.device):
+        _lib.check(_lib.cuda().dl_tc_conv5x5(mode, act.data_ptr(), w.data_ptr(), out.data_ptr(),
+                                             bias.data_ptr() if bias is not None else None, B, H, W, cin, cout, int(split_k), 0,
+                                             int(terms), _stream(act)))
+    return out
+
+
+class _Conv5x5Implicit(torch.autograd.Function):
+    """Forward / dgrad / wgrad as implicit GEMMs: no im2col, col2im or transposed buffer at all."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, terms):
+        x = x.contiguous()
+        B, H, W, C = x.shape
+        cout = weight.shape[0]
+        M = B * H * W
+        bn = 64 if cout <= 64 else 128
+        y = torch.empty(M, cout, dtype=torch.float32, device=x.device)
+        _tc_conv(1, x, weight, y, bias, B, H, W, C, cout, _splits((M + 127) // 128, (cout + bn - 1) // bn, TAPS * C), terms)
+        ctx.save_for_backward(x, weight)
+        ctx.meta = (terms, bias is not None)
+        return y.view(B, H, W, cout)
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, weight = ctx.saved_tensors
+        terms, has_bias = ctx.meta
+        B, H, W, C = x.shape
+        cout, kc = weight.shape
+        M = B * H * W
+        dy = dy.contiguous()
+        dx = dw = db = None
+        if ctx.needs_input_grad[1]:
+            dw = torch.empty(cout, kc, dtype=torch.float32, device=x.device)
+            _tc_conv(3, x, dy, dw, None, B, H, W, C, cout, _splits((cout + 127) // 128, (kc + 127) // 128, M), terms)
+        if has_bias and ctx.needs_input_grad[2]:
+            db = dy.view(M, cout).sum(0)
+        if ctx.needs_input_grad[0]:
+            bn = 64 if C <= 64 else 128
+            dx = torch.empty(B, H, W, C, dtype=torch.float32, device=x.device)
+            _tc_conv(2, dy, weight, dx, None, B, H, W, C, cout, _splits((M + 127) // 128, (C + bn - 1) // bn, TAPS * cout), terms)
+        return dx, dw, db, None
+
+
 class _Conv5x5(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, weight, bias, terms):
@@ -96,18 +158,22 @@ class _Conv5x5(torch.autograd.Function):
         return dx, dw, db, None
 
 
-def conv5x5_nhwc(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor] = None, terms: int = 3) -> torch.Tensor:
+def conv5x5_nhwc(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor] = None, terms: int = 3,
+                  implicit: Optional[bool] = None) -> torch.Tensor:
     """x [B,H,W,Cin] NHWC, weight [Cout, 25*Cin] with columns ordered (kh, kw, cin) -> y [B,H,W,Cout]."""
-    return _Conv5x5.apply(x, weight, bias, terms)
+    B, H, W, C = x.shape
+    if implicit is None:
+        implicit = _implicit_ok(B, H, W, C, weight.shape[0])
+    return (_Conv5x5Implicit if implicit else _Conv5x5).apply(x, weight, bias, terms)
 
 
 class TCConv5x5(torch.nn.Module):
     """``nn.Conv2d(cin, cout, 5, 1, 2)`` with NHWC activations and the weight kept as the GEMM operand
     ``[cout, 25*cin]`` ((kh, kw, cin) column order).  Same initialisation distribution as nn.Conv2d."""
 
-    def __init__(self, cin: int, cout: int, terms: int = 3):
+    def __init__(self, cin: int, cout: int, terms: int = 3, implicit: Optional[bool] = None):
         super().__init__()
-        self.cin, self.cout, self.terms = cin, cout, terms
+        self.cin, self.cout, self.terms, self.implicit = cin, cout, terms, implicit
         self.weight = torch.nn.Parameter(torch.empty(cout, TAPS * cin))
         self.bias = torch.nn.Parameter(torch.empty(cout))
         bound = 1.0 / math.sqrt(cin * TAPS)
@@ -115,7 +181,7 @@ class TCConv5x5(torch.nn.Module):
         torch.nn.init.uniform_(self.bias, -bound, bound)
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
-        return conv5x5_nhwc(x, self.weight, self.bias, self.terms)
+        return conv5x5_nhwc(x, self.weight, self.bias, self.terms, self.implicit)
 
     @torch.no_grad()
     def load_conv2d(self, conv: torch.nn.Conv2d) -> None:

@@ -41,6 +41,8 @@ class TrainStep:
         self.loss_host = torch.zeros((), dtype=torch.float32).pin_memory() if dev.type == "cuda" else torch.zeros(())
         self.graph: Optional[torch.cuda.CUDAGraph] = None
         self.launches_per_step = 0
+        self.kernels_per_step = 0
+        self._replayed_kernels = 0
         self.use_graph = bool(use_graph and dev.type == "cuda")
         self._warmup = warmup
         self._captured = False
@@ -65,10 +67,22 @@ class TrainStep:
             self.sgd.step(self.flat, lr=self.lr, momentum=self.momentum, weight_decay=self.weight_decay,
                           nesterov=self.nesterov, zero_grads=True, variant=self.variant, nblocks=self.nblocks)
 
+    def _native_count(self) -> int:
+        if self.device.type != "cuda":
+            return self.sgd.comm.launches
+        from .. import _lib
+        return int(_lib.cuda().dl_kernel_launches())
+
     def _eager(self) -> None:
-        before = self.sgd.comm.launches
+        before, nbefore = self.sgd.comm.launches, self._native_count()
         self._body()
         self.launches_per_step = self.sgd.comm.launches - before
+        self.kernels_per_step = self._native_count() - nbefore      # collectives + tensor-core convolutions + helpers
+
+    @property
+    def kernel_launches(self) -> int:
+        """Kernels of this library launched so far (host-counted launches + kernels replayed inside CUDA graphs)."""
+        return self._native_count() + self._replayed_kernels
 
     def capture(self) -> None:
         """Warm up eagerly on the current contents of the static buffers (loads modules, lets cuDNN
@@ -89,11 +103,12 @@ class TrainStep:
         if not self.use_graph:
             return
         self.graph = torch.cuda.CUDAGraph()
-        steps_before, launches_before = self.sgd.steps, self.sgd.comm.launches
+        steps_before, launches_before, native_before = self.sgd.steps, self.sgd.comm.launches, self._native_count()
         with torch.cuda.graph(self.graph):
             self._body()
         # the capture itself did not execute a step
         self.sgd.steps, self.sgd.comm.launches = steps_before, launches_before
+        self._replayed_kernels -= self._native_count() - native_before
         torch.cuda.synchronize(self.device)
 
     # ------------------------------------------------------------------------------------------------
@@ -110,6 +125,7 @@ class TrainStep:
             self.graph.replay()
             self.sgd.steps += 1
             self.sgd.comm.launches += self.launches_per_step
+            self._replayed_kernels += self.kernels_per_step
         else:
             self._eager()
         return self.loss
