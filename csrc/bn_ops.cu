@@ -1,0 +1,315 @@
+// Fused SpatialBatchNormalization (training mode) + ReLU + 2x2/2 max-pooling on NHWC activations,
+// forward and backward — the elementwise tail of every block of the reference's CIFAR network
+// (examples/Model.lua:21-24: batch-norm eps 1e-3, ReLU, SpatialMaxPooling(2,2,2,2)).
+//
+// Done op by op this tail streams each activation ~17 times per step; here it is read twice in the
+// forward pass (statistics, then normalise + ReLU + pool, writing only the pooled quarter) and twice
+// in the backward pass (per-channel reductions, then the input gradient), with the ReLU mask and the
+// arg-max of each window recomputed from the saved conv output instead of being stored.
+//
+//   forward   stats : sum, sum of squares per channel                      -> mean, invstd (+ running statistics)
+//             apply : p[b,h/2,w/2,c] = max_{2x2} relu(gamma * (y - mean) * invstd + beta)
+//   backward  reduce: dz = dp routed to the window arg-max where z > 0;  sum dz, sum dz * xhat per channel
+//             apply : dy = gamma * invstd * (dz - mean(dz) - xhat * mean(dz * xhat));  dgamma, dbeta
+#include "dl_common.cuh"
+#include "dl_host.h"
+
+#define BN_THREADS 256
+
+// per-channel accumulators, double so that partial sums from thousands of threads add up accurately
+struct BnWork {
+  double* sum;    // [C]
+  double* sumsq;  // [C]
+};
+
+// ---- forward statistics --------------------------------------------------------------------------
+// Thread t of a block owns channel group cg = t % C4 (4 channels) and walks rows r0 + t / C4, stepping by
+// rows_per_pass; block partials are combined through shared memory, one double atomicAdd per channel per block.
+__global__ void __launch_bounds__(BN_THREADS) bn_stats_kernel(const float4* __restrict__ y, long long M, int C4, double* sum,
+                                                              double* sumsq) {
+  extern __shared__ float4 sh[];  // [2][BN_THREADS]
+  const int cg = threadIdx.x % C4;
+  const int lane_row = threadIdx.x / C4;
+  const int rows_per_pass = BN_THREADS / C4;
+  float4 s = make_float4(0.f, 0.f, 0.f, 0.f), q = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (lane_row < rows_per_pass) {
+    for (long long r = static_cast<long long>(blockIdx.x) * rows_per_pass + lane_row; r < M;
+         r += static_cast<long long>(gridDim.x) * rows_per_pass) {
+      const float4 v = y[r * C4 + cg];
+      s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+      q.x += v.x * v.x; q.y += v.y * v.y; q.z += v.z * v.z; q.w += v.w * v.w;
+    }
+  }
+  sh[threadIdx.x] = s;
+  sh[BN_THREADS + threadIdx.x] = q;
+  __syncthreads();
+  if (threadIdx.x < C4) {
+    double ds[4] = {0, 0, 0, 0}, dq[4] = {0, 0, 0, 0};
+    for (int k = 0; k < rows_per_pass; ++k) {
+      const float4 a = sh[k * C4 + threadIdx.x], b = sh[BN_THREADS + k * C4 + threadIdx.x];
+      ds[0] += a.x; ds[1] += a.y; ds[2] += a.z; ds[3] += a.w;
+      dq[0] += b.x; dq[1] += b.y; dq[2] += b.z; dq[3] += b.w;
+    }
+    for (int e = 0; e < 4; ++e) {
+      atomicAdd(&sum[threadIdx.x * 4 + e], ds[e]);
+      atomicAdd(&sumsq[threadIdx.x * 4 + e], dq[e]);
+    }
+  }
+}
+
+// mean / invstd from the sums; running statistics like nn.BatchNorm2d (momentum, unbiased variance)
+__global__ void bn_finalize_kernel(const double* sum, const double* sumsq, long long M, int C, float eps, float momentum,
+                                   float* mean, float* invstd, float* running_mean, float* running_var) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  const double m = sum[c] / static_cast<double>(M);
+  double var = sumsq[c] / static_cast<double>(M) - m * m;
+  if (var < 0) var = 0;
+  mean[c] = static_cast<float>(m);
+  invstd[c] = static_cast<float>(1.0 / sqrt(var + static_cast<double>(eps)));
+  if (running_mean) running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * static_cast<float>(m);
+  if (running_var) {
+    const double unbiased = M > 1 ? var * static_cast<double>(M) / static_cast<double>(M - 1) : var;
+    running_var[c] = (1.f - momentum) * running_var[c] + momentum * static_cast<float>(unbiased);
+  }
+}
+
+__device__ __forceinline__ float4 bn_affine(const float4& v, const float4& sc, const float4& sh) {
+  return make_float4(fmaf(v.x, sc.x, sh.x), fmaf(v.y, sc.y, sh.y), fmaf(v.z, sc.z, sh.z), fmaf(v.w, sc.w, sh.w));
+}
+
+// ---- forward apply: one thread = one pooled output pixel x 4 channels ------------------------------
+__global__ void __launch_bounds__(BN_THREADS) bn_relu_pool_fwd_kernel(const float4* __restrict__ y, float4* __restrict__ p,
+                                                                      const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                                      const float* __restrict__ mean, const float* __restrict__ invstd,
+                                                                      int B, int H, int W, int C4) {
+  const int Ho = H / 2, Wo = W / 2;
+  const long long total = static_cast<long long>(B) * Ho * Wo * C4;
+  for (long long idx = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; idx < total;
+       idx += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int cg = static_cast<int>(idx % C4);
+    long long t = idx / C4;
+    const int wo = static_cast<int>(t % Wo);
+    t /= Wo;
+    const int ho = static_cast<int>(t % Ho);
+    const long long b = t / Ho;
+    const float4 g = reinterpret_cast<const float4*>(gamma)[cg], be = reinterpret_cast<const float4*>(beta)[cg];
+    const float4 mu = reinterpret_cast<const float4*>(mean)[cg], is = reinterpret_cast<const float4*>(invstd)[cg];
+    const float4 sc = make_float4(g.x * is.x, g.y * is.y, g.z * is.z, g.w * is.w);
+    const float4 sh = make_float4(be.x - mu.x * sc.x, be.y - mu.y * sc.y, be.z - mu.z * sc.z, be.w - mu.w * sc.w);
+    const long long base = ((b * H + 2 * ho) * W + 2 * wo) * C4 + cg;
+    float4 m = make_float4(0.f, 0.f, 0.f, 0.f);  // relu floor
+#pragma unroll
+    for (int dh = 0; dh < 2; ++dh)
+#pragma unroll
+      for (int dw = 0; dw < 2; ++dw) {
+        const float4 z = bn_affine(y[base + (static_cast<long long>(dh) * W + dw) * C4], sc, sh);
+        m.x = fmaxf(m.x, z.x); m.y = fmaxf(m.y, z.y); m.z = fmaxf(m.z, z.z); m.w = fmaxf(m.w, z.w);
+      }
+    p[idx] = m;
+  }
+}
+
+// dz of the four window positions for one channel: the pooled gradient goes to the FIRST position (row-major)
+// holding the window maximum, and only if that maximum is positive (ReLU) — the convention of max_pool2d.
+__device__ __forceinline__ void route(const float z[4], float dp, float dz[4]) {
+  int best = 0;
+  float bv = z[0];
+#pragma unroll
+  for (int k = 1; k < 4; ++k)
+    if (z[k] > bv) { bv = z[k]; best = k; }
+#pragma unroll
+  for (int k = 0; k < 4; ++k) dz[k] = (k == best && bv > 0.f) ? dp : 0.f;
+}
+
+// ---- backward reduce: per-channel sum of dz and of dz * xhat ----------------------------------------
+__global__ void __launch_bounds__(BN_THREADS) bn_relu_pool_bwd_reduce_kernel(const float4* __restrict__ y, const float4* __restrict__ dp,
+                                                                             const float* __restrict__ gamma,
+                                                                             const float* __restrict__ beta,
+                                                                             const float* __restrict__ mean,
+                                                                             const float* __restrict__ invstd, int B, int H, int W,
+                                                                             int C4, double* sum_dz, double* sum_dzx) {
+  extern __shared__ float4 sh[];
+  const int Ho = H / 2, Wo = W / 2;
+  const long long windows = static_cast<long long>(B) * Ho * Wo;
+  const int cg = threadIdx.x % C4;
+  const int lane_row = threadIdx.x / C4;
+  const int rows_per_pass = BN_THREADS / C4;
+  const float4 g = reinterpret_cast<const float4*>(gamma)[cg], be = reinterpret_cast<const float4*>(beta)[cg];
+  const float4 mu = reinterpret_cast<const float4*>(mean)[cg], is = reinterpret_cast<const float4*>(invstd)[cg];
+  const float gs[4] = {g.x * is.x, g.y * is.y, g.z * is.z, g.w * is.w};
+  const float bs[4] = {be.x - mu.x * gs[0], be.y - mu.y * gs[1], be.z - mu.z * gs[2], be.w - mu.w * gs[3]};
+  const float mus[4] = {mu.x, mu.y, mu.z, mu.w}, iss[4] = {is.x, is.y, is.z, is.w};
+  float s[4] = {0.f, 0.f, 0.f, 0.f}, q[4] = {0.f, 0.f, 0.f, 0.f};
+  if (lane_row < rows_per_pass) {
+    for (long long wi = static_cast<long long>(blockIdx.x) * rows_per_pass + lane_row; wi < windows;
+         wi += static_cast<long long>(gridDim.x) * rows_per_pass) {
+      const int wo = static_cast<int>(wi % Wo);
+      const long long t = wi / Wo;
+      const int ho = static_cast<int>(t % Ho);
+      const long long b = t / Ho;
+      const long long base = ((b * H + 2 * ho) * W + 2 * wo) * C4 + cg;
+      float4 v[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) v[k] = y[base + (static_cast<long long>(k >> 1) * W + (k & 1)) * C4];
+      const float4 d = dp[wi * C4 + cg];
+      const float dpe[4] = {d.x, d.y, d.z, d.w};
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        float ye[4], z[4], dz[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          ye[k] = e == 0 ? v[k].x : e == 1 ? v[k].y : e == 2 ? v[k].z : v[k].w;
+          z[k] = fmaf(ye[k], gs[e], bs[e]);
+        }
+        route(z, dpe[e], dz);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          s[e] += dz[k];
+          q[e] += dz[k] * (ye[k] - mus[e]) * iss[e];
+        }
+      }
+    }
+  }
+  sh[threadIdx.x] = make_float4(s[0], s[1], s[2], s[3]);
+  sh[BN_THREADS + threadIdx.x] = make_float4(q[0], q[1], q[2], q[3]);
+  __syncthreads();
+  if (threadIdx.x < C4) {
+    double ds[4] = {0, 0, 0, 0}, dq[4] = {0, 0, 0, 0};
+    for (int k = 0; k < rows_per_pass; ++k) {
+      const float4 a = sh[k * C4 + threadIdx.x], b = sh[BN_THREADS + k * C4 + threadIdx.x];
+      ds[0] += a.x; ds[1] += a.y; ds[2] += a.z; ds[3] += a.w;
+      dq[0] += b.x; dq[1] += b.y; dq[2] += b.z; dq[3] += b.w;
+    }
+    for (int e = 0; e < 4; ++e) {
+      atomicAdd(&sum_dz[threadIdx.x * 4 + e], ds[e]);
+      atomicAdd(&sum_dzx[threadIdx.x * 4 + e], dq[e]);
+    }
+  }
+}
+
+// ---- backward apply: dy for the four positions of each window; block 0 also writes dgamma / dbeta ------
+__global__ void __launch_bounds__(BN_THREADS) bn_relu_pool_bwd_apply_kernel(const float4* __restrict__ y, const float4* __restrict__ dp,
+                                                                            float4* __restrict__ dy, const float* __restrict__ gamma,
+                                                                            const float* __restrict__ beta,
+                                                                            const float* __restrict__ mean,
+                                                                            const float* __restrict__ invstd, int B, int H, int W,
+                                                                            int C4, const double* sum_dz, const double* sum_dzx,
+                                                                            float* dgamma, float* dbeta) {
+  const int Ho = H / 2, Wo = W / 2;
+  const long long windows = static_cast<long long>(B) * Ho * Wo;
+  const double invM = 1.0 / (static_cast<double>(windows) * 4.0);
+  if (blockIdx.x == 0) {
+    for (int c = threadIdx.x; c < C4 * 4; c += blockDim.x) {
+      dgamma[c] = static_cast<float>(sum_dzx[c]);
+      dbeta[c] = static_cast<float>(sum_dz[c]);
+    }
+  }
+  const long long total = windows * C4;
+  for (long long idx = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; idx < total;
+       idx += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int cg = static_cast<int>(idx % C4);
+    const long long wi = idx / C4;
+    const int wo = static_cast<int>(wi % Wo);
+    const long long t = wi / Wo;
+    const int ho = static_cast<int>(t % Ho);
+    const long long b = t / Ho;
+    const float4 g = reinterpret_cast<const float4*>(gamma)[cg], be = reinterpret_cast<const float4*>(beta)[cg];
+    const float4 mu = reinterpret_cast<const float4*>(mean)[cg], is = reinterpret_cast<const float4*>(invstd)[cg];
+    const float gs[4] = {g.x * is.x, g.y * is.y, g.z * is.z, g.w * is.w};
+    const float bs[4] = {be.x - mu.x * gs[0], be.y - mu.y * gs[1], be.z - mu.z * gs[2], be.w - mu.w * gs[3]};
+    const float mus[4] = {mu.x, mu.y, mu.z, mu.w}, iss[4] = {is.x, is.y, is.z, is.w};
+    const long long base = ((b * H + 2 * ho) * W + 2 * wo) * C4 + cg;
+    float4 v[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) v[k] = y[base + (static_cast<long long>(k >> 1) * W + (k & 1)) * C4];
+    const float4 d = dp[idx];
+    const float dpe[4] = {d.x, d.y, d.z, d.w};
+    float out[4][4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const float m_dz = static_cast<float>(sum_dz[cg * 4 + e] * invM), m_dzx = static_cast<float>(sum_dzx[cg * 4 + e] * invM);
+      float ye[4], z[4], dz[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        ye[k] = e == 0 ? v[k].x : e == 1 ? v[k].y : e == 2 ? v[k].z : v[k].w;
+        z[k] = fmaf(ye[k], gs[e], bs[e]);
+      }
+      route(z, dpe[e], dz);
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const float xhat = (ye[k] - mus[e]) * iss[e];
+        out[k][e] = gs[e] * (dz[k] - m_dz - xhat * m_dzx);
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+      dy[base + (static_cast<long long>(k >> 1) * W + (k & 1)) * C4] = make_float4(out[k][0], out[k][1], out[k][2], out[k][3]);
+  }
+}
+
+static int bn_grid(long long items, int per_block) {
+  long long nb = (items + per_block - 1) / per_block;
+  const long long cap = static_cast<long long>(dl_sm_count()) * 8;
+  if (nb > cap) nb = cap;
+  return nb < 1 ? 1 : static_cast<int>(nb);
+}
+
+extern "C" size_t dl_bn_work_bytes(int C) { return static_cast<size_t>(C) * 2 * sizeof(double); }
+
+// y [B,H,W,C] -> p [B,H/2,W/2,C]; writes mean/invstd [C] (saved for backward) and updates the running statistics.
+// work: dl_bn_work_bytes(C) bytes of device scratch (zeroed here).
+extern "C" int dl_bn_relu_pool_fwd(const float* y, float* p, const float* gamma, const float* beta, float* mean, float* invstd,
+                                   float* running_mean, float* running_var, int B, int H, int W, int C, float eps, float momentum,
+                                   void* work, void* stream) {
+  DL_REQUIRE(y && p && gamma && beta && mean && invstd && work, "dl_bn_relu_pool_fwd: null pointer");
+  DL_REQUIRE(C % 4 == 0 && C / 4 <= BN_THREADS && H % 2 == 0 && W % 2 == 0, "dl_bn_relu_pool_fwd: need C %% 4 == 0, C <= %d, even H and W",
+             BN_THREADS * 4);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const long long M = static_cast<long long>(B) * H * W;
+  const int C4 = C / 4;
+  double* sum = static_cast<double*>(work);
+  double* sumsq = sum + C;
+  DL_CUDA(cudaMemsetAsync(work, 0, dl_bn_work_bytes(C), st));
+  const int rows_per_pass = BN_THREADS / C4;
+  bn_stats_kernel<<<bn_grid(M, rows_per_pass * 16), BN_THREADS, 2 * BN_THREADS * sizeof(float4), st>>>(
+      reinterpret_cast<const float4*>(y), M, C4, sum, sumsq);
+  dl_note_launch();
+  DL_CUDA(cudaGetLastError());
+  bn_finalize_kernel<<<(C + 127) / 128, 128, 0, st>>>(sum, sumsq, M, C, eps, momentum, mean, invstd, running_mean, running_var);
+  dl_note_launch();
+  DL_CUDA(cudaGetLastError());
+  const long long items = M / 4 * C4;
+  bn_relu_pool_fwd_kernel<<<bn_grid(items, BN_THREADS), BN_THREADS, 0, st>>>(reinterpret_cast<const float4*>(y),
+                                                                              reinterpret_cast<float4*>(p), gamma, beta, mean,
+                                                                              invstd, B, H, W, C4);
+  dl_note_launch();
+  DL_CUDA(cudaGetLastError());
+  return DL_OK;
+}
+
+// dp [B,H/2,W/2,C] -> dy [B,H,W,C], dgamma [C], dbeta [C]; y, mean, invstd as saved by the forward call.
+extern "C" int dl_bn_relu_pool_bwd(const float* y, const float* dp, float* dy, const float* gamma, const float* beta,
+                                   const float* mean, const float* invstd, float* dgamma, float* dbeta, int B, int H, int W, int C,
+                                   void* work, void* stream) {
+  DL_REQUIRE(y && dp && dy && gamma && beta && mean && invstd && dgamma && dbeta && work, "dl_bn_relu_pool_bwd: null pointer");
+  DL_REQUIRE(C % 4 == 0 && C / 4 <= BN_THREADS && H % 2 == 0 && W % 2 == 0, "dl_bn_relu_pool_bwd: need C %% 4 == 0, C <= %d, even H and W",
+             BN_THREADS * 4);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int C4 = C / 4;
+  const long long windows = static_cast<long long>(B) * (H / 2) * (W / 2);
+  double* sum_dz = static_cast<double*>(work);
+  double* sum_dzx = sum_dz + C;
+  DL_CUDA(cudaMemsetAsync(work, 0, dl_bn_work_bytes(C), st));
+  const int rows_per_pass = BN_THREADS / C4;
+  bn_relu_pool_bwd_reduce_kernel<<<bn_grid(windows, rows_per_pass * 8), BN_THREADS, 2 * BN_THREADS * sizeof(float4), st>>>(
+      reinterpret_cast<const float4*>(y), reinterpret_cast<const float4*>(dp), gamma, beta, mean, invstd, B, H, W, C4, sum_dz, sum_dzx);
+  dl_note_launch();
+  DL_CUDA(cudaGetLastError());
+  bn_relu_pool_bwd_apply_kernel<<<bn_grid(windows * C4, BN_THREADS), BN_THREADS, 0, st>>>(
+      reinterpret_cast<const float4*>(y), reinterpret_cast<const float4*>(dp), reinterpret_cast<float4*>(dy), gamma, beta, mean, invstd,
+      B, H, W, C4, sum_dz, sum_dzx, dgamma, dbeta);
+  dl_note_launch();
+  DL_CUDA(cudaGetLastError());
+  return DL_OK;
+}

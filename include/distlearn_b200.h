@@ -192,6 +192,17 @@ int dl_tc_conv5x5(int mode, const float* act, const float* w, float* out, const 
 int dl_im2col5x5(const float* x, float* col, int B, int H, int W, int C, long long ld, void* stream);
 int dl_col2im5x5(const float* dcol, float* dx, int B, int H, int W, int C, long long ld, void* stream);
 
+/* Fused training-mode batch-norm + ReLU + 2x2/2 max-pool on NHWC fp32 activations, forward and backward
+ * (SpatialBatchNormalization(eps 1e-3) -> ReLU -> SpatialMaxPooling(2,2,2,2), examples/Model.lua:21-24).
+ * y [B,H,W,C] -> p [B,H/2,W/2,C]; mean/invstd [C] are outputs of the forward call and inputs of the backward
+ * one; running_mean/var (may be NULL) are updated like nn.BatchNorm2d.  work: dl_bn_work_bytes(C) bytes. */
+size_t dl_bn_work_bytes(int C);
+int dl_bn_relu_pool_fwd(const float* y, float* p, const float* gamma, const float* beta, float* mean, float* invstd,
+                        float* running_mean, float* running_var, int B, int H, int W, int C, float eps, float momentum,
+                        void* work, void* stream);
+int dl_bn_relu_pool_bwd(const float* y, const float* dp, float* dy, const float* gamma, const float* beta, const float* mean,
+                        const float* invstd, float* dgamma, float* dbeta, int B, int H, int W, int C, void* work, void* stream);
+
 /* ---- local flat-vector ops (single GPU, no communication) ---- */
 /* p -= lr * (g*scale [+ wd*p] [momentum]); optionally zero g. world==1 fast path. */
 int dl_local_sgd(float* p, float* g, float* m, uint64_t n, float lr, float momentum,

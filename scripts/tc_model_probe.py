@@ -39,7 +39,9 @@ def bench(model, iters=20, graph=True):
 
 
 for name, mk, tf32 in [("cuDNN fp32", lambda: cifar_convnet(0), False), ("cuDNN tf32", lambda: cifar_convnet(0), True),
-                       ("tcgen05 3xTF32", lambda: cifar_convnet_tc(0, 3), False), ("tcgen05 TF32", lambda: cifar_convnet_tc(0, 1), False)]:
+                       ("tcgen05 3xTF32, torch BN/ReLU/pool", lambda: cifar_convnet_tc(0, 3, fused_tail=False), False),
+                       ("tcgen05 3xTF32 + fused BN/ReLU/pool", lambda: cifar_convnet_tc(0, 3), False),
+                       ("tcgen05 TF32 + fused BN/ReLU/pool", lambda: cifar_convnet_tc(0, 1), False)]:
     torch.backends.cudnn.allow_tf32 = tf32
     m = mk().to(dev)
     print(f"{name}: fwd+bwd {bench(m):.3f} ms/step at batch {B}", flush=True)

@@ -35,6 +35,7 @@ CUDA_SOURCES = [
     "local_ops.cu",
     "tc_gemm.cu",
     "conv_ops.cu",
+    "bn_ops.cu",
 ]
 HOST_SOURCES = ["host_transport.cpp"]
 

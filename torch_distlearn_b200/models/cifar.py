@@ -38,19 +38,25 @@ class CifarConvNetTC(nn.Module):
     features in the reference's (c, h, w) order, so ``load_reference`` maps parameters one to one."""
     CHANNELS = CifarConvNet.CHANNELS
 
-    def __init__(self, terms: int = 3):
+    def __init__(self, terms: int = 3, fused_tail: bool = True):
         super().__init__()
+        from ..ops.bn import FusedBNReLUPool
         from ..ops.conv import TCConv5x5
+        self.fused_tail = fused_tail
         self.convs = nn.ModuleList([TCConv5x5(cin, cout, terms) for cin, cout in zip(self.CHANNELS[:-1], self.CHANNELS[1:])])
-        self.bns = nn.ModuleList([nn.BatchNorm2d(c, eps=1e-3) for c in self.CHANNELS[1:]])
+        self.bns = nn.ModuleList([FusedBNReLUPool(c, eps=1e-3) if fused_tail else nn.BatchNorm2d(c, eps=1e-3)
+                                  for c in self.CHANNELS[1:]])
         self.linear = nn.Linear(512 * 2 * 2, 10)
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         x = x.permute(0, 2, 3, 1).contiguous()                     # NCHW input batch -> NHWC once
         for conv, bn in zip(self.convs, self.bns):
-            y = conv(x).permute(0, 3, 1, 2)                        # NHWC data seen as a channels_last NCHW tensor
-            y = F.max_pool2d(F.relu(bn(y)), 2, 2)                  # cuDNN / ATen channels_last kernels
-            x = y.permute(0, 2, 3, 1)                              # contiguous NHWC again (no copy)
+            if self.fused_tail:
+                x = bn(conv(x))                                    # BN + ReLU + 2x2 max-pool in one pair of passes (csrc/bn_ops.cu)
+            else:
+                y = conv(x).permute(0, 3, 1, 2)                    # NHWC data seen as a channels_last NCHW tensor
+                y = F.max_pool2d(F.relu(bn(y)), 2, 2)              # cuDNN / ATen channels_last kernels
+                x = y.permute(0, 2, 3, 1)                          # contiguous NHWC again (no copy)
         x = self.linear(x.permute(0, 3, 1, 2).reshape(x.shape[0], 2048))   # (c, h, w) feature order, examples/Model.lua:44
         return F.log_softmax(x, dim=1)
 
@@ -64,9 +70,9 @@ class CifarConvNetTC(nn.Module):
         return self
 
 
-def cifar_convnet_tc(seed: int = 0, terms: int = 3) -> CifarConvNetTC:
+def cifar_convnet_tc(seed: int = 0, terms: int = 3, fused_tail: bool = True) -> CifarConvNetTC:
     """Same initial weights as ``cifar_convnet(seed)`` (built from it), convolutions on tcgen05."""
-    return CifarConvNetTC(terms).load_reference(cifar_convnet(seed))
+    return CifarConvNetTC(terms, fused_tail).load_reference(cifar_convnet(seed))
 
 
 def cifar_convnet(seed: int = 0) -> CifarConvNet:

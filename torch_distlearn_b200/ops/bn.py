@@ -1,0 +1,73 @@
+"""Fused training-mode BatchNorm + ReLU + 2x2 max-pool on NHWC activations (csrc/bn_ops.cu): the
+elementwise tail of each block of the reference's CIFAR network (examples/Model.lua:21-24) in two
+passes over the activation forward and two backward, instead of one pass per op."""
+from __future__ import annotations
+
+import torch
+import torch.nn.functional as F
+
+from .. import _lib
+
+
+def _stream(t: torch.Tensor) -> int:
+    return torch.cuda.current_stream(t.device).cuda_stream
+
+
+class _BNReLUPool(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, y, gamma, beta, running_mean, running_var, eps, momentum):
+        y = y.contiguous()
+        B, H, W, C = y.shape
+        p = torch.empty(B, H // 2, W // 2, C, dtype=torch.float32, device=y.device)
+        mean = torch.empty(C, dtype=torch.float32, device=y.device)
+        invstd = torch.empty(C, dtype=torch.float32, device=y.device)
+        work = torch.empty(2 * C, dtype=torch.float64, device=y.device)
+        with torch.cuda.device(y.device):
+            _lib.check(_lib.cuda().dl_bn_relu_pool_fwd(
+                y.data_ptr(), p.data_ptr(), gamma.data_ptr(), beta.data_ptr(), mean.data_ptr(), invstd.data_ptr(),
+                running_mean.data_ptr() if running_mean is not None else None,
+                running_var.data_ptr() if running_var is not None else None, B, H, W, C, float(eps), float(momentum),
+                work.data_ptr(), _stream(y)))
+        ctx.save_for_backward(y, gamma, beta, mean, invstd)
+        return p
+
+    @staticmethod
+    def backward(ctx, dp):
+        y, gamma, beta, mean, invstd = ctx.saved_tensors
+        B, H, W, C = y.shape
+        dp = dp.contiguous()
+        dy = torch.empty_like(y)
+        dgamma = torch.empty(C, dtype=torch.float32, device=y.device)
+        dbeta = torch.empty(C, dtype=torch.float32, device=y.device)
+        work = torch.empty(2 * C, dtype=torch.float64, device=y.device)
+        with torch.cuda.device(y.device):
+            _lib.check(_lib.cuda().dl_bn_relu_pool_bwd(
+                y.data_ptr(), dp.data_ptr(), dy.data_ptr(), gamma.data_ptr(), beta.data_ptr(), mean.data_ptr(), invstd.data_ptr(),
+                dgamma.data_ptr(), dbeta.data_ptr(), B, H, W, C, work.data_ptr(), _stream(y)))
+        return dy, dgamma, dbeta, None, None, None, None
+
+
+class FusedBNReLUPool(torch.nn.Module):
+    """``max_pool2d(relu(BatchNorm2d(C, eps)(x)), 2, 2)`` on NHWC tensors ``[B, H, W, C] -> [B, H/2, W/2, C]``.
+    Parameters and buffers carry the names of ``nn.BatchNorm2d`` so state dicts are interchangeable."""
+
+    def __init__(self, channels: int, eps: float = 1e-3, momentum: float = 0.1):
+        super().__init__()
+        self.channels, self.eps, self.momentum = channels, eps, momentum
+        self.weight = torch.nn.Parameter(torch.ones(channels))
+        self.bias = torch.nn.Parameter(torch.zeros(channels))
+        self.register_buffer("running_mean", torch.zeros(channels))
+        self.register_buffer("running_var", torch.ones(channels))
+        self.register_buffer("num_batches_tracked", torch.tensor(0, dtype=torch.long))
+
+    def forward(self, y: torch.Tensor) -> torch.Tensor:
+        if self.training and y.is_cuda:
+            # (num_batches_tracked is not advanced: it only matters for momentum=None, and a host-side
+            # counter update would be one more tiny kernel per layer per step)
+            return _BNReLUPool.apply(y, self.weight, self.bias, self.running_mean, self.running_var, self.eps, self.momentum)
+        z = F.batch_norm(y.permute(0, 3, 1, 2), self.running_mean, self.running_var, self.weight, self.bias, self.training,
+                         self.momentum, self.eps)
+        return F.max_pool2d(F.relu(z), 2, 2).permute(0, 2, 3, 1)
+
+    def extra_repr(self) -> str:
+        return f"{self.channels}, eps={self.eps}, momentum={self.momentum}, fused=BN+ReLU+MaxPool2x2 (NHWC)"

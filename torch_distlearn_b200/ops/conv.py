@@ -54,11 +54,20 @@ def col2im5x5(dcol: torch.Tensor, shape) -> torch.Tensor:
     return dx
 
 
-def _splits(m_tiles: int, n_tiles: int, k: int, sms: int = 148) -> int:
-    """Split K so that roughly two waves of CTAs exist, keeping >= 128 K (4 K-blocks) per split."""
+def _splits(m_tiles: int, n_tiles: int, k: int, sms: int = 148, overhead_kb: int = 6) -> int:
+    """K-split that minimises  waves x (K-blocks per CTA + fixed per-CTA cost)  for a one-CTA-per-SM kernel:
+    few output tiles need many splits to fill the 148 SMs, and the number of CTAs should land just under a
+    whole number of waves.  Every split keeps at least 4 K-blocks (K = 128)."""
     tiles = max(m_tiles * n_tiles, 1)
-    want = max(1, (2 * sms + tiles - 1) // tiles)
-    return max(1, min(want, k // 128))
+    kb = max((k + 31) // 32, 1)
+    best, best_cost = 1, None
+    for s in range(1, max(1, kb // 4) + 1):
+        per = (kb + s - 1) // s
+        ctas = tiles * ((kb + per - 1) // per)
+        cost = ((ctas + sms - 1) // sms) * (per + overhead_kb)
+        if best_cost is None or cost < best_cost:
+            best, best_cost = s, cost
+    return best
 
 
 def _implicit_ok(B: int, H: int, W: int, cin: int, cout: int) -> bool:
