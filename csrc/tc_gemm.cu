@@ -117,6 +117,25 @@ __device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t desc_a, uint
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "elect.sync _|p, 0xffffffff;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(pred));
+  return pred != 0;
+}
+// explicit shared-space 128-bit accesses (a generic pointer derived from the aligned dynamic-smem base makes the
+// compiler emit generic LD/ST, which are slower than LDS/STS)
+__device__ __forceinline__ float4 lds128(uint32_t addr) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ void sts128(uint32_t addr, const float4& v) {
+  asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
 __device__ __forceinline__ float tf32_round(float x) {
   uint32_t r;
   asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
@@ -248,66 +267,75 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
       // instruction descriptor: D = fp32, A = B = TF32, both K-major, N = BN, M = 128
       const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | (static_cast<uint32_t>(BN >> 3) << 17) |
                              (static_cast<uint32_t>(BM >> 4) << 24) | (g.a_mn ? (1u << 15) : 0u) | (g.b_mn ? (1u << 16) : 0u);
+      // Everything below is computed by all 32 lanes with warp-uniform values, so descriptors live in uniform
+      // registers; only the tcgen05 instructions themselves are issued by one elected lane.  (Computing them
+      // under `if (lane == 0)` costs a register->uniform-register move per operand per MMA and made the issue
+      // loop, not the tensor core, the bottleneck.)
+      const uint32_t a_base = smem_u32(&s.a[0][0][0]), b_base = smem_u32(&s.b[0][0][0]);
+      constexpr uint32_t A_TILE = BM * BK * 4, B_TILE = BN * BK * 4;   // bytes of one hi (or lo) tile
+      const uint64_t a_step = g.a_mn ? (1024 >> 4) : ((UMMA_K * 4) >> 4);  // one K step (8 elements) in 16-byte units
+      const uint64_t b_step = g.b_mn ? (1024 >> 4) : ((UMMA_K * 4) >> 4);
+      const bool three = g.terms == 3;
+      int st = 0, it = 0;
       for (int i = 0; i < nkb; ++i) {
-        const int st = i % STAGES, it = i / STAGES;
         const int chunk = i / CHUNK, buf = chunk & 1, use = chunk >> 1;
         const bool first_in_chunk = (i % CHUNK) == 0, last_in_chunk = (i % CHUNK) == CHUNK - 1 || i == nkb - 1;
         if (first_in_chunk) mbar_wait(&s.acc_empty[buf], (use & 1) ^ 1);   // drain warps are done with this buffer
         mbar_wait(&s.conv[st], it & 1);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        if (lane == 0) {
-          const uint32_t acc = tmem + static_cast<uint32_t>(buf * BN);
-          const uint32_t pa_hi = smem_u32(&s.a[st][0][0]), pa_lo = smem_u32(&s.a[st][1][0]);
-          const uint32_t pb_hi = smem_u32(&s.b[st][0][0]), pb_lo = smem_u32(&s.b[st][1][0]);
-          const uint64_t a_hi = g.a_mn ? make_desc_mn(pa_hi) : make_desc(pa_hi), a_lo = g.a_mn ? make_desc_mn(pa_lo) : make_desc(pa_lo);
-          const uint64_t b_hi = g.b_mn ? make_desc_mn(pb_hi) : make_desc(pb_hi), b_lo = g.b_mn ? make_desc_mn(pb_lo) : make_desc(pb_lo);
-          // one K step (8 elements): K-major = 32 bytes along the swizzled row, MN-major = the next 8-row group (1024 bytes)
-          const uint64_t a_step = g.a_mn ? (1024 >> 4) : ((UMMA_K * 4) >> 4), b_step = g.b_mn ? (1024 >> 4) : ((UMMA_K * 4) >> 4);
+        const uint32_t acc = tmem + static_cast<uint32_t>(buf * BN);
+        const uint32_t pa_hi = a_base + static_cast<uint32_t>(st) * 2 * A_TILE, pa_lo = pa_hi + A_TILE;
+        const uint32_t pb_hi = b_base + static_cast<uint32_t>(st) * 2 * B_TILE, pb_lo = pb_hi + B_TILE;
+        const uint64_t a_hi = g.a_mn ? make_desc_mn(pa_hi) : make_desc(pa_hi), a_lo = g.a_mn ? make_desc_mn(pa_lo) : make_desc(pa_lo);
+        const uint64_t b_hi = g.b_mn ? make_desc_mn(pb_hi) : make_desc(pb_hi), b_lo = g.b_mn ? make_desc_mn(pb_lo) : make_desc(pb_lo);
+        const uint32_t keep0 = first_in_chunk ? 0u : 1u;                    // a new chunk overwrites its buffer
+        if (elect_one()) {
+          if (three) {
 #pragma unroll
-          for (int k = 0; k < BK / UMMA_K; ++k) {
-            const uint64_t aa = a_step * k, bb = b_step * k;
-            const uint32_t keep = (first_in_chunk && k == 0) ? 0u : 1u;          // a new chunk overwrites its buffer
-            if (g.terms == 3) {
+            for (int k = 0; k < BK / UMMA_K; ++k) {
               // small terms first, the dominant product last
-              umma_tf32(acc, a_lo + aa, b_hi + bb, idesc, keep);
-              umma_tf32(acc, a_hi + aa, b_lo + bb, idesc, 1u);
-              umma_tf32(acc, a_hi + aa, b_hi + bb, idesc, 1u);
-            } else {
-              umma_tf32(acc, a_hi + aa, b_hi + bb, idesc, keep);
+              umma_tf32(acc, a_lo + a_step * k, b_hi + b_step * k, idesc, k == 0 ? keep0 : 1u);
+              umma_tf32(acc, a_hi + a_step * k, b_lo + b_step * k, idesc, 1u);
+              umma_tf32(acc, a_hi + a_step * k, b_hi + b_step * k, idesc, 1u);
             }
+          } else {
+#pragma unroll
+            for (int k = 0; k < BK / UMMA_K; ++k) umma_tf32(acc, a_hi + a_step * k, b_hi + b_step * k, idesc, k == 0 ? keep0 : 1u);
           }
           umma_commit(&s.empty[st]);                          // stage reusable once these MMAs have read it
           if (last_in_chunk) umma_commit(&s.acc_full[buf]);   // chunk complete: hand the buffer to the drain warps
         }
         __syncwarp();
+        if (++st == STAGES) { st = 0; ++it; }
       }
     } else if (warp < 6) {
       // ===== converters (warps 2..5, 128 threads) =====
       const int t = threadIdx.x - 64;
+      const uint32_t a_base = smem_u32(&s.a[0][0][0]), b_base = smem_u32(&s.b[0][0][0]);
+      constexpr uint32_t A_TILE = BM * BK * 4, B_TILE = BN * BK * 4;
+      const bool three = g.terms == 3;
+      int st = 0, it = 0;
       for (int i = 0; i < nkb; ++i) {
-        const int st = i % STAGES, it = i / STAGES;
         mbar_wait(&s.full[st], it & 1);
-        float4* a_hi = reinterpret_cast<float4*>(&s.a[st][0][0]);
-        float4* a_lo = reinterpret_cast<float4*>(&s.a[st][1][0]);
-        float4* b_hi = reinterpret_cast<float4*>(&s.b[st][0][0]);
-        float4* b_lo = reinterpret_cast<float4*>(&s.b[st][1][0]);
-        const bool three = g.terms == 3;
-#pragma unroll 4
-        for (int j = t; j < BM * BK / 4; j += 128) {
-          const float4 v = a_hi[j];
+        const uint32_t a_hi = a_base + static_cast<uint32_t>(st) * 2 * A_TILE + t * 16, a_lo = a_hi + A_TILE;
+        const uint32_t b_hi = b_base + static_cast<uint32_t>(st) * 2 * B_TILE + t * 16, b_lo = b_hi + B_TILE;
+#pragma unroll
+        for (int j = 0; j < BM * BK / 4 / 128; ++j) {
+          const float4 v = lds128(a_hi + j * 2048);
           const float4 h = make_float4(tf32_round(v.x), tf32_round(v.y), tf32_round(v.z), tf32_round(v.w));
-          a_hi[j] = h;
-          if (three) a_lo[j] = make_float4(v.x - h.x, v.y - h.y, v.z - h.z, v.w - h.w);
+          sts128(a_hi + j * 2048, h);
+          if (three) sts128(a_lo + j * 2048, make_float4(v.x - h.x, v.y - h.y, v.z - h.z, v.w - h.w));
         }
-#pragma unroll 4
-        for (int j = t; j < BN * BK / 4; j += 128) {
-          const float4 v = b_hi[j];
+#pragma unroll
+        for (int j = 0; j < BN * BK / 4 / 128; ++j) {
+          const float4 v = lds128(b_hi + j * 2048);
           const float4 h = make_float4(tf32_round(v.x), tf32_round(v.y), tf32_round(v.z), tf32_round(v.w));
-          b_hi[j] = h;
-          if (three) b_lo[j] = make_float4(v.x - h.x, v.y - h.y, v.z - h.z, v.w - h.w);
+          sts128(b_hi + j * 2048, h);
+          if (three) sts128(b_lo + j * 2048, make_float4(v.x - h.x, v.y - h.y, v.z - h.z, v.w - h.w));
         }
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy writes -> visible to the tensor core
         mbar_arrive(&s.conv[st]);
+        if (++st == STAGES) { st = 0; ++it; }
       }
     } else {
       // ===== drain + epilogue (warps 6..9): this warp owns TMEM lanes [32*(warp%4), +32) = output rows =====
