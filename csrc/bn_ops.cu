@@ -16,17 +16,11 @@
 
 #define BN_THREADS 256
 
-// per-channel accumulators, double so that partial sums from thousands of threads add up accurately
-struct BnWork {
-  double* sum;    // [C]
-  double* sumsq;  // [C]
-};
-
 // ---- forward statistics --------------------------------------------------------------------------
 // Thread t of a block owns channel group cg = t % C4 (4 channels) and walks rows r0 + t / C4, stepping by
-// rows_per_pass; block partials are combined through shared memory, one double atomicAdd per channel per block.
-__global__ void __launch_bounds__(BN_THREADS) bn_stats_kernel(const float4* __restrict__ y, long long M, int C4, double* sum,
-                                                              double* sumsq) {
+// rows_per_pass; block partials are combined through shared memory and written out per block (no atomics).
+__global__ void __launch_bounds__(BN_THREADS) bn_stats_kernel(const float4* __restrict__ y, long long M, int C4,
+                                                              float4* __restrict__ partial) {
   extern __shared__ float4 sh[];  // [2][BN_THREADS]
   const int cg = threadIdx.x % C4;
   const int lane_row = threadIdx.x / C4;
@@ -44,26 +38,30 @@ __global__ void __launch_bounds__(BN_THREADS) bn_stats_kernel(const float4* __re
   sh[BN_THREADS + threadIdx.x] = q;
   __syncthreads();
   if (threadIdx.x < C4) {
-    double ds[4] = {0, 0, 0, 0}, dq[4] = {0, 0, 0, 0};
+    float4 ds = make_float4(0.f, 0.f, 0.f, 0.f), dq = make_float4(0.f, 0.f, 0.f, 0.f);
     for (int k = 0; k < rows_per_pass; ++k) {
       const float4 a = sh[k * C4 + threadIdx.x], b = sh[BN_THREADS + k * C4 + threadIdx.x];
-      ds[0] += a.x; ds[1] += a.y; ds[2] += a.z; ds[3] += a.w;
-      dq[0] += b.x; dq[1] += b.y; dq[2] += b.z; dq[3] += b.w;
+      ds.x += a.x; ds.y += a.y; ds.z += a.z; ds.w += a.w;
+      dq.x += b.x; dq.y += b.y; dq.z += b.z; dq.w += b.w;
     }
-    for (int e = 0; e < 4; ++e) {
-      atomicAdd(&sum[threadIdx.x * 4 + e], ds[e]);
-      atomicAdd(&sumsq[threadIdx.x * 4 + e], dq[e]);
-    }
+    // per-block partial sums; the finalize kernel adds them in a fixed order (deterministic, no atomics)
+    partial[(static_cast<long long>(blockIdx.x) * 2 + 0) * C4 + threadIdx.x] = ds;
+    partial[(static_cast<long long>(blockIdx.x) * 2 + 1) * C4 + threadIdx.x] = dq;
   }
 }
 
 // mean / invstd from the sums; running statistics like nn.BatchNorm2d (momentum, unbiased variance)
-__global__ void bn_finalize_kernel(const double* sum, const double* sumsq, long long M, int C, float eps, float momentum,
+__global__ void bn_finalize_kernel(const float* partial, int nblocks, long long M, int C, float eps, float momentum,
                                    float* mean, float* invstd, float* running_mean, float* running_var) {
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= C) return;
-  const double m = sum[c] / static_cast<double>(M);
-  double var = sumsq[c] / static_cast<double>(M) - m * m;
+  double sum = 0.0, sumsq = 0.0;
+  for (int b = 0; b < nblocks; ++b) {
+    sum += static_cast<double>(partial[(static_cast<long long>(b) * 2 + 0) * C + c]);
+    sumsq += static_cast<double>(partial[(static_cast<long long>(b) * 2 + 1) * C + c]);
+  }
+  const double m = sum / static_cast<double>(M);
+  double var = sumsq / static_cast<double>(M) - m * m;
   if (var < 0) var = 0;
   mean[c] = static_cast<float>(m);
   invstd[c] = static_cast<float>(1.0 / sqrt(var + static_cast<double>(eps)));
@@ -128,7 +126,7 @@ __global__ void __launch_bounds__(BN_THREADS) bn_relu_pool_bwd_reduce_kernel(con
                                                                              const float* __restrict__ beta,
                                                                              const float* __restrict__ mean,
                                                                              const float* __restrict__ invstd, int B, int H, int W,
-                                                                             int C4, double* sum_dz, double* sum_dzx) {
+                                                                             int C4, float4* __restrict__ partial) {
   extern __shared__ float4 sh[];
   const int Ho = H / 2, Wo = W / 2;
   const long long windows = static_cast<long long>(B) * Ho * Wo;
@@ -175,36 +173,42 @@ __global__ void __launch_bounds__(BN_THREADS) bn_relu_pool_bwd_reduce_kernel(con
   sh[BN_THREADS + threadIdx.x] = make_float4(q[0], q[1], q[2], q[3]);
   __syncthreads();
   if (threadIdx.x < C4) {
-    double ds[4] = {0, 0, 0, 0}, dq[4] = {0, 0, 0, 0};
+    float4 ds = make_float4(0.f, 0.f, 0.f, 0.f), dq = make_float4(0.f, 0.f, 0.f, 0.f);
     for (int k = 0; k < rows_per_pass; ++k) {
       const float4 a = sh[k * C4 + threadIdx.x], b = sh[BN_THREADS + k * C4 + threadIdx.x];
-      ds[0] += a.x; ds[1] += a.y; ds[2] += a.z; ds[3] += a.w;
-      dq[0] += b.x; dq[1] += b.y; dq[2] += b.z; dq[3] += b.w;
+      ds.x += a.x; ds.y += a.y; ds.z += a.z; ds.w += a.w;
+      dq.x += b.x; dq.y += b.y; dq.z += b.z; dq.w += b.w;
     }
-    for (int e = 0; e < 4; ++e) {
-      atomicAdd(&sum_dz[threadIdx.x * 4 + e], ds[e]);
-      atomicAdd(&sum_dzx[threadIdx.x * 4 + e], dq[e]);
-    }
+    partial[(static_cast<long long>(blockIdx.x) * 2 + 0) * C4 + threadIdx.x] = ds;
+    partial[(static_cast<long long>(blockIdx.x) * 2 + 1) * C4 + threadIdx.x] = dq;
   }
 }
 
-// ---- backward apply: dy for the four positions of each window; block 0 also writes dgamma / dbeta ------
+// sums of the per-block partials of the backward reduction -> sum_dz, sum_dzx (double), dgamma, dbeta
+__global__ void bn_bwd_finalize_kernel(const float* partial, int nblocks, int C, double* sums, float* dgamma, float* dbeta) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  double a = 0.0, b = 0.0;
+  for (int k = 0; k < nblocks; ++k) {
+    a += static_cast<double>(partial[(static_cast<long long>(k) * 2 + 0) * C + c]);
+    b += static_cast<double>(partial[(static_cast<long long>(k) * 2 + 1) * C + c]);
+  }
+  sums[c] = a;
+  sums[C + c] = b;
+  dbeta[c] = static_cast<float>(a);
+  dgamma[c] = static_cast<float>(b);
+}
+
+// ---- backward apply: dy for the four positions of each window ----------------------------------------
 __global__ void __launch_bounds__(BN_THREADS) bn_relu_pool_bwd_apply_kernel(const float4* __restrict__ y, const float4* __restrict__ dp,
                                                                             float4* __restrict__ dy, const float* __restrict__ gamma,
                                                                             const float* __restrict__ beta,
                                                                             const float* __restrict__ mean,
                                                                             const float* __restrict__ invstd, int B, int H, int W,
-                                                                            int C4, const double* sum_dz, const double* sum_dzx,
-                                                                            float* dgamma, float* dbeta) {
+                                                                            int C4, const double* sum_dz, const double* sum_dzx) {
   const int Ho = H / 2, Wo = W / 2;
   const long long windows = static_cast<long long>(B) * Ho * Wo;
   const double invM = 1.0 / (static_cast<double>(windows) * 4.0);
-  if (blockIdx.x == 0) {
-    for (int c = threadIdx.x; c < C4 * 4; c += blockDim.x) {
-      dgamma[c] = static_cast<float>(sum_dzx[c]);
-      dbeta[c] = static_cast<float>(sum_dz[c]);
-    }
-  }
   const long long total = windows * C4;
   for (long long idx = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; idx < total;
        idx += static_cast<long long>(gridDim.x) * blockDim.x) {
@@ -255,28 +259,39 @@ static int bn_grid(long long items, int per_block) {
   return nb < 1 ? 1 : static_cast<int>(nb);
 }
 
-extern "C" size_t dl_bn_work_bytes(int C) { return static_cast<size_t>(C) * 2 * sizeof(double); }
+// reductions use one block per SM pair at most: each block leaves one partial row, summed by a finalize kernel
+#define BN_MAX_REDUCE_BLOCKS 296
+static int bn_reduce_grid(long long rows, int rows_per_pass) {
+  long long nb = (rows + static_cast<long long>(rows_per_pass) * 8 - 1) / (static_cast<long long>(rows_per_pass) * 8);
+  if (nb > BN_MAX_REDUCE_BLOCKS) nb = BN_MAX_REDUCE_BLOCKS;
+  return nb < 1 ? 1 : static_cast<int>(nb);
+}
+
+// scratch: per-block partial sums (float) followed by 2*C doubles
+extern "C" size_t dl_bn_work_bytes(int C) {
+  return static_cast<size_t>(BN_MAX_REDUCE_BLOCKS) * 2 * C * sizeof(float) + static_cast<size_t>(C) * 2 * sizeof(double);
+}
 
 // y [B,H,W,C] -> p [B,H/2,W/2,C]; writes mean/invstd [C] (saved for backward) and updates the running statistics.
-// work: dl_bn_work_bytes(C) bytes of device scratch (zeroed here).
+// work: dl_bn_work_bytes(C) bytes of device scratch (no initialisation needed).
 extern "C" int dl_bn_relu_pool_fwd(const float* y, float* p, const float* gamma, const float* beta, float* mean, float* invstd,
                                    float* running_mean, float* running_var, int B, int H, int W, int C, float eps, float momentum,
                                    void* work, void* stream) {
   DL_REQUIRE(y && p && gamma && beta && mean && invstd && work, "dl_bn_relu_pool_fwd: null pointer");
   DL_REQUIRE(C % 4 == 0 && C / 4 <= BN_THREADS && H % 2 == 0 && W % 2 == 0, "dl_bn_relu_pool_fwd: need C %% 4 == 0, C <= %d, even H and W",
              BN_THREADS * 4);
+  DL_REQUIRE(reinterpret_cast<uintptr_t>(work) % 16 == 0, "dl_bn_relu_pool_fwd: work must be 16-byte aligned");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const long long M = static_cast<long long>(B) * H * W;
   const int C4 = C / 4;
-  double* sum = static_cast<double*>(work);
-  double* sumsq = sum + C;
-  DL_CUDA(cudaMemsetAsync(work, 0, dl_bn_work_bytes(C), st));
+  float* partial = static_cast<float*>(work);
   const int rows_per_pass = BN_THREADS / C4;
-  bn_stats_kernel<<<bn_grid(M, rows_per_pass * 16), BN_THREADS, 2 * BN_THREADS * sizeof(float4), st>>>(
-      reinterpret_cast<const float4*>(y), M, C4, sum, sumsq);
+  const int nb = bn_reduce_grid(M, rows_per_pass);
+  bn_stats_kernel<<<nb, BN_THREADS, 2 * BN_THREADS * sizeof(float4), st>>>(reinterpret_cast<const float4*>(y), M, C4,
+                                                                         reinterpret_cast<float4*>(partial));
   dl_note_launch();
   DL_CUDA(cudaGetLastError());
-  bn_finalize_kernel<<<(C + 127) / 128, 128, 0, st>>>(sum, sumsq, M, C, eps, momentum, mean, invstd, running_mean, running_var);
+  bn_finalize_kernel<<<(C + 127) / 128, 128, 0, st>>>(partial, nb, M, C, eps, momentum, mean, invstd, running_mean, running_var);
   dl_note_launch();
   DL_CUDA(cudaGetLastError());
   const long long items = M / 4 * C4;
@@ -295,20 +310,78 @@ extern "C" int dl_bn_relu_pool_bwd(const float* y, const float* dp, float* dy, c
   DL_REQUIRE(y && dp && dy && gamma && beta && mean && invstd && dgamma && dbeta && work, "dl_bn_relu_pool_bwd: null pointer");
   DL_REQUIRE(C % 4 == 0 && C / 4 <= BN_THREADS && H % 2 == 0 && W % 2 == 0, "dl_bn_relu_pool_bwd: need C %% 4 == 0, C <= %d, even H and W",
              BN_THREADS * 4);
+  DL_REQUIRE(reinterpret_cast<uintptr_t>(work) % 16 == 0, "dl_bn_relu_pool_bwd: work must be 16-byte aligned");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const int C4 = C / 4;
   const long long windows = static_cast<long long>(B) * (H / 2) * (W / 2);
-  double* sum_dz = static_cast<double*>(work);
-  double* sum_dzx = sum_dz + C;
-  DL_CUDA(cudaMemsetAsync(work, 0, dl_bn_work_bytes(C), st));
+  float* partial = static_cast<float*>(work);
+  double* sums = reinterpret_cast<double*>(partial + static_cast<size_t>(BN_MAX_REDUCE_BLOCKS) * 2 * C);
   const int rows_per_pass = BN_THREADS / C4;
-  bn_relu_pool_bwd_reduce_kernel<<<bn_grid(windows, rows_per_pass * 8), BN_THREADS, 2 * BN_THREADS * sizeof(float4), st>>>(
-      reinterpret_cast<const float4*>(y), reinterpret_cast<const float4*>(dp), gamma, beta, mean, invstd, B, H, W, C4, sum_dz, sum_dzx);
+  const int nb = bn_reduce_grid(windows, rows_per_pass);
+  bn_relu_pool_bwd_reduce_kernel<<<nb, BN_THREADS, 2 * BN_THREADS * sizeof(float4), st>>>(
+      reinterpret_cast<const float4*>(y), reinterpret_cast<const float4*>(dp), gamma, beta, mean, invstd, B, H, W, C4,
+      reinterpret_cast<float4*>(partial));
+  dl_note_launch();
+  DL_CUDA(cudaGetLastError());
+  bn_bwd_finalize_kernel<<<(C + 127) / 128, 128, 0, st>>>(partial, nb, C, sums, dgamma, dbeta);
   dl_note_launch();
   DL_CUDA(cudaGetLastError());
   bn_relu_pool_bwd_apply_kernel<<<bn_grid(windows * C4, BN_THREADS), BN_THREADS, 0, st>>>(
       reinterpret_cast<const float4*>(y), reinterpret_cast<const float4*>(dp), reinterpret_cast<float4*>(dy), gamma, beta, mean, invstd,
-      B, H, W, C4, sum_dz, sum_dzx, dgamma, dbeta);
+      B, H, W, C4, sums, sums + C);
+  dl_note_launch();
+  DL_CUDA(cudaGetLastError());
+  return DL_OK;
+}
+
+// Column sums of a row-major [M, C] fp32 matrix (the convolution's bias gradient, sum over pixels of dY):
+// same two-stage reduction.  work: dl_bn_work_bytes(C) bytes.
+__global__ void __launch_bounds__(BN_THREADS) colsum_kernel(const float4* __restrict__ x, long long M, int C4, float4* __restrict__ partial) {
+  extern __shared__ float4 sh[];
+  const int cg = threadIdx.x % C4;
+  const int lane_row = threadIdx.x / C4;
+  const int rows_per_pass = BN_THREADS / C4;
+  float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (lane_row < rows_per_pass) {
+    for (long long r = static_cast<long long>(blockIdx.x) * rows_per_pass + lane_row; r < M;
+         r += static_cast<long long>(gridDim.x) * rows_per_pass) {
+      const float4 v = x[r * C4 + cg];
+      s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+    }
+  }
+  sh[threadIdx.x] = s;
+  __syncthreads();
+  if (threadIdx.x < C4) {
+    float4 ds = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int k = 0; k < rows_per_pass; ++k) {
+      const float4 a = sh[k * C4 + threadIdx.x];
+      ds.x += a.x; ds.y += a.y; ds.z += a.z; ds.w += a.w;
+    }
+    partial[static_cast<long long>(blockIdx.x) * C4 + threadIdx.x] = ds;
+  }
+}
+
+__global__ void colsum_finalize_kernel(const float* partial, int nblocks, int C, float* out) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  double a = 0.0;
+  for (int k = 0; k < nblocks; ++k) a += static_cast<double>(partial[static_cast<long long>(k) * C + c]);
+  out[c] = static_cast<float>(a);
+}
+
+extern "C" int dl_colsum(const float* x, float* out, long long M, int C, void* work, void* stream) {
+  DL_REQUIRE(x && out && work && M > 0, "dl_colsum: bad arguments");
+  DL_REQUIRE(C % 4 == 0 && C / 4 <= BN_THREADS, "dl_colsum: need C %% 4 == 0 and C <= %d", BN_THREADS * 4);
+  DL_REQUIRE(reinterpret_cast<uintptr_t>(x) % 16 == 0 && reinterpret_cast<uintptr_t>(work) % 16 == 0, "dl_colsum: 16-byte alignment required");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int C4 = C / 4;
+  const int rows_per_pass = BN_THREADS / C4;
+  const int nb = bn_reduce_grid(M, rows_per_pass);
+  colsum_kernel<<<nb, BN_THREADS, BN_THREADS * sizeof(float4), st>>>(reinterpret_cast<const float4*>(x), M, C4,
+                                                                   reinterpret_cast<float4*>(work));
+  dl_note_launch();
+  DL_CUDA(cudaGetLastError());
+  colsum_finalize_kernel<<<(C + 127) / 128, 128, 0, st>>>(static_cast<const float*>(work), nb, C, out);
   dl_note_launch();
   DL_CUDA(cudaGetLastError());
   return DL_OK;

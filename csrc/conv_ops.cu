@@ -40,6 +40,34 @@ __global__ void __launch_bounds__(256) im2col5x5_kernel(const float* __restrict_
   }
 }
 
+// Any C (the first layer has C = 3): one thread produces four consecutive columns of a col row (four scalar
+// gathers, one 16-byte store), so the 40 MB col matrix of layer 1 is written with full-width stores.
+__global__ void __launch_bounds__(256) im2col5x5_gather4_kernel(const float* __restrict__ x, float* __restrict__ col, int B, int H,
+                                                                int W, int C, long long ld) {
+  const long long row_items = ld / 4;
+  const long long total = static_cast<long long>(B) * H * W * row_items;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  const int kc = CONV_TAPS * C;
+  for (long long idx = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; idx < total; idx += stride) {
+    const long long m = idx / row_items;
+    const int k0 = static_cast<int>(idx - m * row_items) * 4;
+    const int w = static_cast<int>(m % W);
+    const long long t = m / W;
+    const int h = static_cast<int>(t % H);
+    const long long b = t / H;
+    float v[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const int k = k0 + e;
+      const int tap = k / C, c = k - tap * C;
+      const int hi = h + tap / CONV_K - CONV_PAD, wi = w + tap % CONV_K - CONV_PAD;
+      const bool in = k < kc && hi >= 0 && hi < H && wi >= 0 && wi < W;
+      v[e] = in ? __ldg(x + ((b * H + hi) * W + wi) * C + c) : 0.f;
+    }
+    reinterpret_cast<float4*>(col)[idx] = make_float4(v[0], v[1], v[2], v[3]);
+  }
+}
+
 template <int VEC>
 __global__ void __launch_bounds__(256) col2im5x5_kernel(const float* __restrict__ dcol, float* __restrict__ dx, int B, int H, int W,
                                                         int C, long long ld) {
@@ -89,8 +117,10 @@ extern "C" int dl_im2col5x5(const float* x, float* col, int B, int H, int W, int
   DL_REQUIRE(ld >= static_cast<long long>(CONV_TAPS) * C, "dl_im2col5x5: ld %lld is smaller than 25*C", ld);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const bool vec = C % 4 == 0 && ld % 4 == 0 && reinterpret_cast<uintptr_t>(x) % 16 == 0 && reinterpret_cast<uintptr_t>(col) % 16 == 0;
-  const long long items = static_cast<long long>(B) * H * W * (vec ? ld / 4 : ld);
+  const bool gather4 = !vec && ld % 4 == 0 && reinterpret_cast<uintptr_t>(col) % 16 == 0;
+  const long long items = static_cast<long long>(B) * H * W * ((vec || gather4) ? ld / 4 : ld);
   if (vec) im2col5x5_kernel<4><<<conv_grid(items), 256, 0, st>>>(x, col, B, H, W, C, ld);
+  else if (gather4) im2col5x5_gather4_kernel<<<conv_grid(items), 256, 0, st>>>(x, col, B, H, W, C, ld);
   else im2col5x5_kernel<1><<<conv_grid(items), 256, 0, st>>>(x, col, B, H, W, C, ld);
   dl_note_launch();
   DL_CUDA(cudaGetLastError());

@@ -13,6 +13,18 @@ def _stream(t: torch.Tensor) -> int:
     return torch.cuda.current_stream(t.device).cuda_stream
 
 
+def colsum(x: torch.Tensor) -> torch.Tensor:
+    """Column sums of a contiguous [M, C] fp32 CUDA matrix (C % 4 == 0): the bias gradient of a convolution."""
+    M, C = x.shape
+    if not (x.is_cuda and x.is_contiguous() and x.dtype == torch.float32 and C % 4 == 0 and C <= 1024):
+        return x.sum(0)
+    out = torch.empty(C, dtype=torch.float32, device=x.device)
+    work = torch.empty(int(_lib.cuda().dl_bn_work_bytes(C)) // 8 + 1, dtype=torch.float64, device=x.device)
+    with torch.cuda.device(x.device):
+        _lib.check(_lib.cuda().dl_colsum(x.data_ptr(), out.data_ptr(), M, C, work.data_ptr(), _stream(x)))
+    return out
+
+
 class _BNReLUPool(torch.autograd.Function):
     @staticmethod
     def forward(ctx, y, gamma, beta, running_mean, running_var, eps, momentum):
@@ -21,7 +33,7 @@ class _BNReLUPool(torch.autograd.Function):
         p = torch.empty(B, H // 2, W // 2, C, dtype=torch.float32, device=y.device)
         mean = torch.empty(C, dtype=torch.float32, device=y.device)
         invstd = torch.empty(C, dtype=torch.float32, device=y.device)
-        work = torch.empty(2 * C, dtype=torch.float64, device=y.device)
+        work = torch.empty(int(_lib.cuda().dl_bn_work_bytes(C)) // 8 + 1, dtype=torch.float64, device=y.device)
         with torch.cuda.device(y.device):
             _lib.check(_lib.cuda().dl_bn_relu_pool_fwd(
                 y.data_ptr(), p.data_ptr(), gamma.data_ptr(), beta.data_ptr(), mean.data_ptr(), invstd.data_ptr(),
@@ -39,7 +51,7 @@ class _BNReLUPool(torch.autograd.Function):
         dy = torch.empty_like(y)
         dgamma = torch.empty(C, dtype=torch.float32, device=y.device)
         dbeta = torch.empty(C, dtype=torch.float32, device=y.device)
-        work = torch.empty(2 * C, dtype=torch.float64, device=y.device)
+        work = torch.empty(int(_lib.cuda().dl_bn_work_bytes(C)) // 8 + 1, dtype=torch.float64, device=y.device)
         with torch.cuda.device(y.device):
             _lib.check(_lib.cuda().dl_bn_relu_pool_bwd(
                 y.data_ptr(), dp.data_ptr(), dy.data_ptr(), gamma.data_ptr(), beta.data_ptr(), mean.data_ptr(), invstd.data_ptr(),

@@ -119,7 +119,8 @@ class _Conv5x5Implicit(torch.autograd.Function):
             dw = torch.empty(cout, kc, dtype=torch.float32, device=x.device)
             _tc_conv(3, x, dy, dw, None, B, H, W, C, cout, _splits((cout + 127) // 128, (kc + 127) // 128, M), terms)
         if has_bias and ctx.needs_input_grad[2]:
-            db = dy.view(M, cout).sum(0)
+            from .bn import colsum
+            db = colsum(dy.view(M, cout))
         if ctx.needs_input_grad[0]:
             bn = 64 if C <= 64 else 128
             dx = torch.empty(B, H, W, C, dtype=torch.float32, device=x.device)
@@ -160,7 +161,8 @@ class _Conv5x5(torch.autograd.Function):
                               split_k=_splits((cout + 127) // 128, (ld + bn - 1) // bn, M))
             dw = dw_full[:, :kc] if ld != kc else dw_full
         if has_bias and ctx.needs_input_grad[2]:
-            db = dy2.sum(0)
+            from .bn import colsum
+            db = colsum(dy2)
         if ctx.needs_input_grad[0]:
             dcol = tc_gemm(dy2, w, b_mn=True, terms=terms)          # [M, ld]; K = Cout is short, no split
             dx = col2im5x5(dcol, (B, H, W, C))
