@@ -26,6 +26,7 @@
 #include <cuda.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdlib.h>
 
 #include <mutex>
 #include <unordered_map>
@@ -411,6 +412,329 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
   }
 }
 
+
+// tcgen05.mma with the A operand in tensor memory (lanes = rows of the tile, one 32-bit column per K element)
+__device__ __forceinline__ void umma_tf32_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t}" ::"r"(tmem_d),
+      "r"(tmem_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ float lds32(uint32_t addr) {
+  float v;
+  asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr));
+  return v;
+}
+// 16 consecutive 32-bit columns of this thread's TMEM lane
+__device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t (&r)[16]) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
+      "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};" ::"r"(taddr),
+      "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]), "r"(r[9]), "r"(r[10]),
+      "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15])
+      : "memory");
+}
+// 32 consecutive 32-bit columns of this thread's TMEM lane
+__device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t (&r)[32]) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+      "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
+      "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};" ::"r"(taddr),
+      "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]), "r"(r[9]), "r"(r[10]),
+      "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]), "r"(r[16]), "r"(r[17]), "r"(r[18]), "r"(r[19]), "r"(r[20]),
+      "r"(r[21]), "r"(r[22]), "r"(r[23]), "r"(r[24]), "r"(r[25]), "r"(r[26]), "r"(r[27]), "r"(r[28]), "r"(r[29]), "r"(r[30]),
+      "r"(r[31])
+      : "memory");
+}
+
+// "TS" variant of the kernel: the A operand never returns to shared memory.  The converter warps read each raw A
+// row once from shared memory and write its TF32 hi / lo parts into TENSOR memory (tcgen05.st), from where the
+// MMA takes them; only B still makes the smem -> smem round trip.  Per K block that is 144 KB of shared-memory
+// traffic instead of 224 KB — and the kernel is shared-memory-bandwidth bound — plus a 4-deep ring, because a
+// stage no longer holds an A-lo tile.
+constexpr int TS_STAGES = 4;
+constexpr int TS_THREADS = 576;   // producer, MMA, 8 converter warps, 8 drain warps
+template <int BN>
+struct SmemTS {
+  float a[TS_STAGES][BM * BK];        // raw fp32 A tile (TMA destination)
+  float b[TS_STAGES][2][BN * BK];     // [0] = hi (TMA destination), [1] = lo
+  uint64_t full[TS_STAGES], conv[TS_STAGES], empty[TS_STAGES], acc_full[2], acc_empty[2];
+  uint32_t tmem_base;
+};
+
+template <int BN>
+__global__ void __launch_bounds__(TS_THREADS, 1)
+tc_gemm_ts_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, GemmArgs g) {
+  extern __shared__ __align__(1024) unsigned char smem_raw[];
+  SmemTS<BN>& s = *reinterpret_cast<SmemTS<BN>*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int m0 = blockIdx.x * BM, n0 = blockIdx.y * BN;
+  const int total_kb = (g.K + BK - 1) / BK;
+  const int kb_begin = blockIdx.z * g.kblocks_per_split;
+  int kb_end = kb_begin + g.kblocks_per_split;
+  if (kb_end > total_kb) kb_end = total_kb;
+  const int nkb = kb_end - kb_begin;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < TS_STAGES; ++i) {
+      mbar_init(&s.full[i], 1);
+      mbar_init(&s.conv[i], 256);
+      mbar_init(&s.empty[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&s.acc_full[i], 1);
+      mbar_init(&s.acc_empty[i], 256);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {  // TMEM: two accumulator buffers of BN columns + TS_STAGES x (hi, lo) A tiles of 32 columns: all 512 columns
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s.tmem_base)), "n"(512) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem = s.tmem_base;
+
+  if (nkb > 0) {
+    if (warp == 0) {
+      // ===== TMA producer =====
+      if (lane == 0) {
+        for (int i = 0; i < nkb; ++i) {
+          const int st = i % TS_STAGES, it = i / TS_STAGES;
+          mbar_wait(&s.empty[st], (it & 1) ^ 1);
+          mbar_expect_tx(&s.full[st], (BM + BN) * BK * 4);
+          const int kb = kb_begin + i;
+          const int k0 = kb * BK;
+          if (g.mode == 1 || g.mode == 2) {
+            // A tile = 128 consecutive pixels of the NHWC tensor, shifted by the filter tap of this K block
+            const int hw = g.cH * g.cW;
+            const int b0 = m0 / hw, h0 = (m0 - b0 * hw) / g.cW;
+            const int per_tap = g.cA / BK;
+            const int tap = kb / per_tap, cb = kb - tap * per_tap;
+            int dh = tap / 5 - 2, dw = tap % 5 - 2;
+            if (g.mode == 2) { dh = -dh; dw = -dw; }
+            tma_load_4d(&s.a[st][0], &map_a, &s.full[st], cb * BK, dw, h0 + dh, b0);
+            if (g.mode == 1) {
+              tma_load_2d(&s.b[st][0][0], &map_b, &s.full[st], k0, n0);
+            } else {
+              // W[co, (tap, cin)] as an MN-major operand: rows = this block of 32 output channels, columns = tap*Cin + n
+              for (int bx = 0; bx < BN / 32; ++bx)
+                tma_load_2d(&s.b[st][0][bx * 32 * BK], &map_b, &s.full[st], tap * g.cIn + n0 + 32 * bx, cb * BK);
+            }
+          } else if (g.mode == 3) {
+            for (int bx = 0; bx < BM / 32; ++bx) tma_load_2d(&s.a[st][bx * 32 * BK], &map_a, &s.full[st], m0 + 32 * bx, k0);
+            // B boxes = 32 consecutive pixels (the K block) x 32 channels of one tap, straight from X
+            const int hw = g.cH * g.cW;
+            const int b0 = k0 / hw, h0 = (k0 - b0 * hw) / g.cW;
+            for (int bx = 0; bx < BN / 32; ++bx) {
+              const int col = n0 + 32 * bx;
+              const int tap = col / g.cIn, c0 = col - tap * g.cIn;
+              if (tap < 25) tma_load_4d(&s.b[st][0][bx * 32 * BK], &map_b, &s.full[st], c0, tap % 5 - 2, h0 + tap / 5 - 2, b0);
+              else tma_load_4d(&s.b[st][0][bx * 32 * BK], &map_b, &s.full[st], g.cIn, 0, 0, 0);   // past the last tap: zeros
+            }
+          } else {
+            if (!g.a_mn) {
+              tma_load_2d(&s.a[st][0], &map_a, &s.full[st], k0, m0);
+            } else {
+              for (int bx = 0; bx < BM / 32; ++bx) tma_load_2d(&s.a[st][bx * 32 * BK], &map_a, &s.full[st], m0 + 32 * bx, k0);
+            }
+            if (!g.b_mn) {
+              tma_load_2d(&s.b[st][0][0], &map_b, &s.full[st], k0, n0);
+            } else {
+              for (int bx = 0; bx < BN / 32; ++bx) tma_load_2d(&s.b[st][0][bx * 32 * BK], &map_b, &s.full[st], n0 + 32 * bx, k0);
+            }
+          }
+        }
+      }
+    } else if (warp == 1) {
+      // ===== MMA issuer =====
+      // instruction descriptor: D = fp32, A = B = TF32, both K-major, N = BN, M = 128
+      const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | (static_cast<uint32_t>(BN >> 3) << 17) |
+                             (static_cast<uint32_t>(BM >> 4) << 24) | (g.b_mn ? (1u << 16) : 0u);   // A comes from TMEM (K-major)
+      // Everything below is computed by all 32 lanes with warp-uniform values, so descriptors live in uniform
+      // registers; only the tcgen05 instructions themselves are issued by one elected lane.  (Computing them
+      // under `if (lane == 0)` costs a register->uniform-register move per operand per MMA and made the issue
+      // loop, not the tensor core, the bottleneck.)
+      const uint32_t b_base = smem_u32(&s.b[0][0][0]);
+      constexpr uint32_t B_TILE = BN * BK * 4;                                // bytes of one hi (or lo) B tile
+      const uint64_t b_step = g.b_mn ? (1024 >> 4) : ((UMMA_K * 4) >> 4);      // one K step (8 elements) in 16-byte units
+      const bool three = g.terms == 3;
+      int st = 0, it = 0;
+      for (int i = 0; i < nkb; ++i) {
+        const int chunk = i / CHUNK, buf = chunk & 1, use = chunk >> 1;
+        const bool first_in_chunk = (i % CHUNK) == 0, last_in_chunk = (i % CHUNK) == CHUNK - 1 || i == nkb - 1;
+        if (first_in_chunk) mbar_wait(&s.acc_empty[buf], (use & 1) ^ 1);   // drain warps are done with this buffer
+        mbar_wait(&s.conv[st], it & 1);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        const uint32_t acc = tmem + static_cast<uint32_t>(buf * BN);
+        const uint32_t ta_hi = tmem + static_cast<uint32_t>(2 * BN + st * 64), ta_lo = ta_hi + 32;   // A(hi|lo): 128 lanes x 32 K columns
+        const uint32_t pb_hi = b_base + static_cast<uint32_t>(st) * 2 * B_TILE, pb_lo = pb_hi + B_TILE;
+        const uint64_t b_hi = g.b_mn ? make_desc_mn(pb_hi) : make_desc(pb_hi), b_lo = g.b_mn ? make_desc_mn(pb_lo) : make_desc(pb_lo);
+        const uint32_t keep0 = first_in_chunk ? 0u : 1u;                    // a new chunk overwrites its buffer
+        if (elect_one()) {
+          if (three) {
+#pragma unroll
+            for (int k = 0; k < BK / UMMA_K; ++k) {
+              // small terms first, the dominant product last
+              umma_tf32_ts(acc, ta_lo + k * UMMA_K, b_hi + b_step * k, idesc, k == 0 ? keep0 : 1u);
+              umma_tf32_ts(acc, ta_hi + k * UMMA_K, b_lo + b_step * k, idesc, 1u);
+              umma_tf32_ts(acc, ta_hi + k * UMMA_K, b_hi + b_step * k, idesc, 1u);
+            }
+          } else {
+#pragma unroll
+            for (int k = 0; k < BK / UMMA_K; ++k) umma_tf32_ts(acc, ta_hi + k * UMMA_K, b_hi + b_step * k, idesc, k == 0 ? keep0 : 1u);
+          }
+          umma_commit(&s.empty[st]);                          // stage (smem B, TMEM A, smem raw A) reusable once these MMAs are done
+          if (last_in_chunk) umma_commit(&s.acc_full[buf]);   // chunk complete: hand the buffer to the drain warps
+        }
+        __syncwarp();
+        if (++st == TS_STAGES) { st = 0; ++it; }
+      }
+    } else if (warp < 10) {
+      // ===== converters (warps 2..9, 256 threads: two warps per TMEM lane quarter, each taking half of the K block) =====
+      const int t = threadIdx.x - 64;                     // 0..255
+      const uint32_t a_base = smem_u32(&s.a[0][0]), b_base = smem_u32(&s.b[0][0][0]);
+      constexpr uint32_t A_TILE = BM * BK * 4, B_TILE = BN * BK * 4;
+      const bool three = g.terms == 3;
+      const int quarter = warp & 3;                       // the TMEM lanes this warp may touch: [32*quarter, +32)
+      const int half = (warp - 2) >> 2;                   // which 16 of the 32 K values of the row this warp converts
+      const int row = quarter * 32 + lane;                // = row of the A tile held by this thread
+      int st = 0, it = 0;
+      for (int i = 0; i < nkb; ++i) {
+        mbar_wait(&s.full[st], it & 1);
+        // All shared-memory loads of this K block are issued first (A: 4 x 16 bytes or 16 x 4 bytes of this thread's
+        // row; B: 16 bytes per 4 KB of tile) so that their latencies overlap; conversion and stores follow.
+        const uint32_t a_tile = a_base + static_cast<uint32_t>(st) * A_TILE;
+        const uint32_t b_hi = b_base + static_cast<uint32_t>(st) * 2 * B_TILE + t * 16, b_lo = b_hi + B_TILE;
+        constexpr int NB = BN * BK / 4 / 256;
+        float4 bv[NB];
+        uint32_t hi[16], lo[16];
+        if (!g.a_mn) {
+          // K-major tile, 128-byte rows, 16-byte chunks XOR-swizzled with (row % 8) by the TMA
+          float4 av[4];
+#pragma unroll
+          for (int c = 0; c < 4; ++c) av[c] = lds128(a_tile + row * 128 + (((half * 4 + c) ^ (row & 7)) << 4));
+#pragma unroll
+          for (int j = 0; j < NB; ++j) bv[j] = lds128(b_hi + j * 4096);
+#pragma unroll
+          for (int c = 0; c < 4; ++c) {
+            const float e[4] = {av[c].x, av[c].y, av[c].z, av[c].w};
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+              const float h = tf32_round(e[q]);
+              hi[c * 4 + q] = __float_as_uint(h);
+              lo[c * 4 + q] = __float_as_uint(e[q] - h);
+            }
+          }
+        } else {
+          // MN-major boxes (32 K-rows x 32 rows-of-A, unswizzled): element (k, row) of box row/32
+          const uint32_t colp = a_tile + (row >> 5) * 4096 + (row & 31) * 4 + half * 16 * 128;
+          float e[16];
+#pragma unroll
+          for (int k = 0; k < 16; ++k) e[k] = lds32(colp + k * 128);
+#pragma unroll
+          for (int j = 0; j < NB; ++j) bv[j] = lds128(b_hi + j * 4096);
+#pragma unroll
+          for (int k = 0; k < 16; ++k) {
+            const float h = tf32_round(e[k]);
+            hi[k] = __float_as_uint(h);
+            lo[k] = __float_as_uint(e[k] - h);
+          }
+        }
+        // ---- A -> TMEM lane `row`: columns [16*half, +16) of the stage's hi block, same of its lo block (+32)
+        const uint32_t ta = tmem + (static_cast<uint32_t>(quarter * 32) << 16) + static_cast<uint32_t>(2 * BN + st * 64 + half * 16);
+        tmem_st16(ta, hi);
+        if (three) tmem_st16(ta + 32, lo);
+        // ---- B: hi in place, lo into the sibling tile
+#pragma unroll
+        for (int j = 0; j < NB; ++j) {
+          const float4 v = bv[j];
+          const float4 h = make_float4(tf32_round(v.x), tf32_round(v.y), tf32_round(v.z), tf32_round(v.w));
+          sts128(b_hi + j * 4096, h);
+          if (three) sts128(b_lo + j * 4096, make_float4(v.x - h.x, v.y - h.y, v.z - h.z, v.w - h.w));
+        }
+        asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");   // TMEM stores of this thread are complete
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");    // generic-proxy smem writes -> visible to the tensor core
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+        mbar_arrive(&s.conv[st]);
+        if (++st == TS_STAGES) { st = 0; ++it; }
+      }
+    } else {
+      // ===== drain + epilogue (warps 10..17): warp owns TMEM lanes [32*(warp%4), +32) = output rows and one half of the columns =====
+      const int quarter = warp & 3;
+      const int chalf = (warp - 10) >> 2;
+      constexpr int HN = BN / 2;                           // columns per drain warp
+      const int row = m0 + quarter * 32 + lane;
+      float acc[HN];
+#pragma unroll
+      for (int j = 0; j < HN; ++j) acc[j] = 0.f;
+      const int nchunks = (nkb + CHUNK - 1) / CHUNK;
+      for (int c = 0; c < nchunks; ++c) {
+        const int buf = c & 1, use = c >> 1;
+        mbar_wait(&s.acc_full[buf], use & 1);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+#pragma unroll
+        for (int c0 = 0; c0 < HN; c0 += 16) {
+          uint32_t r[16];
+          const uint32_t taddr = tmem + (static_cast<uint32_t>(quarter * 32) << 16) + static_cast<uint32_t>(buf * BN + chalf * HN + c0);
+          asm volatile(
+              "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+              "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+              : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+                "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+              : "r"(taddr)
+              : "memory");
+          asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+          for (int q = 0; q < 16; ++q) acc[c0 + q] += __uint_as_float(r[q]);
+        }
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+        mbar_arrive(&s.acc_empty[buf]);                      // the MMA warp may overwrite this buffer
+      }
+      if (row < g.M) {
+        float* crow = g.C + static_cast<long long>(row) * g.ldc + n0 + chalf * HN;
+        const bool add_bias = g.bias != nullptr && blockIdx.z == 0;
+#pragma unroll
+        for (int q = 0; q < HN; q += 4) {
+          const int n = n0 + chalf * HN + q;
+          if (n + 3 < g.N && g.vec_out) {
+            float4 v = make_float4(acc[q], acc[q + 1], acc[q + 2], acc[q + 3]);
+            if (add_bias) {
+              const float4 bv = *reinterpret_cast<const float4*>(g.bias + n);
+              v.x += bv.x; v.y += bv.y; v.z += bv.z; v.w += bv.w;
+            }
+            if (g.atomic_out) {
+              asm volatile("red.relaxed.gpu.global.add.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(crow + q), "f"(v.x), "f"(v.y),
+                           "f"(v.z), "f"(v.w)
+                           : "memory");
+            } else {
+              *reinterpret_cast<float4*>(crow + q) = v;
+            }
+          } else {
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              if (n + e < g.N) {
+                float v = acc[q + e];
+                if (add_bias) v += g.bias[n + e];
+                if (g.atomic_out) atomicAdd(crow + q + e, v);
+                else crow[q + e] = v;
+              }
+            }
+          }
+        }
+      }
+    }
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if (warp == 1) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(512) : "memory");
+  }
+}
+
 // ---- host: tensor maps ----------------------------------------------------------------------------
 typedef CUresult (*EncodeTiled_t)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
@@ -463,7 +787,9 @@ int ensure_context() {
 }
 
 // 2-D fp32 row-major matrix [rows, cols] with row pitch ld (elements); box = box_rows x 32 columns, 128B swizzle
-int make_map(CUtensorMap* map, const float* ptr, long long rows, long long cols, long long ld, int box_rows, bool mn_major) {
+// swz: 0 = 128B swizzle (K-major UMMA operand), 1 = 128B swizzle in 32-byte atoms (MN-major TF32 UMMA operand),
+//      2 = none (tile is consumed by threads, not by the tensor core)
+int make_map(CUtensorMap* map, const float* ptr, long long rows, long long cols, long long ld, int box_rows, int swz) {
   DL_REQUIRE(reinterpret_cast<uintptr_t>(ptr) % 16 == 0 && ld % 4 == 0, "tc_gemm: operands must be 16-byte aligned with a row pitch that is a multiple of 4 floats");
   EncodeTiled_t enc = encode_fn();
   DL_REQUIRE(enc != nullptr, "tc_gemm: cuTensorMapEncodeTiled is not available from this driver");
@@ -472,9 +798,9 @@ int make_map(CUtensorMap* map, const float* ptr, long long rows, long long cols,
   cuuint32_t box[2] = {static_cast<cuuint32_t>(BK), static_cast<cuuint32_t>(box_rows)};
   cuuint32_t estr[2] = {1, 1};
   CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(ptr), dims, strides, box, estr,
-                   CU_TENSOR_MAP_INTERLEAVE_NONE, mn_major ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B,
-                   CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
-                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                   CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   swz == 1 ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : swz == 2 ? CU_TENSOR_MAP_SWIZZLE_NONE : CU_TENSOR_MAP_SWIZZLE_128B,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   DL_REQUIRE(r == CUDA_SUCCESS, "tc_gemm: cuTensorMapEncodeTiled failed with CUresult %d (ptr %p rows %lld cols %lld ld %lld)",
              static_cast<int>(r), static_cast<const void*>(ptr), rows, cols, ld);
   return DL_OK;
@@ -504,18 +830,31 @@ int make_map_nhwc(CUtensorMap* map, const float* ptr, int B, int H, int W, int C
   return DL_OK;
 }
 
+// A-in-TMEM ("TS") kernel unless DL_B200_TC_TS=0
+bool use_ts() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("DL_B200_TC_TS");
+    v = (e != nullptr && e[0] == '0') ? 0 : 1;
+  }
+  return v != 0;
+}
+
 template <int BN>
 int launch(const CUtensorMap& ma, const CUtensorMap& mb, const GemmArgs& g, int splits, cudaStream_t st) {
-  static bool configured[64] = {false};
+  static bool configured[2][64] = {{false}};
   int dev = 0;
   DL_CUDA(cudaGetDevice(&dev));
-  const size_t smem = sizeof(Smem<BN>) + 1024;
-  if (dev >= 0 && dev < 64 && !configured[dev]) {
-    DL_CUDA(cudaFuncSetAttribute(tc_gemm_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
-    configured[dev] = true;
+  const bool ts = use_ts();
+  const size_t smem = (ts ? sizeof(SmemTS<BN>) : sizeof(Smem<BN>)) + 1024;
+  if (dev >= 0 && dev < 64 && !configured[ts][dev]) {
+    if (ts) DL_CUDA(cudaFuncSetAttribute(tc_gemm_ts_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+    else DL_CUDA(cudaFuncSetAttribute(tc_gemm_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+    configured[ts][dev] = true;
   }
   dim3 grid((g.M + BM - 1) / BM, (g.N + BN - 1) / BN, splits);
-  tc_gemm_kernel<BN><<<grid, NUM_THREADS, smem, st>>>(ma, mb, g);
+  if (ts) tc_gemm_ts_kernel<BN><<<grid, TS_THREADS, smem, st>>>(ma, mb, g);
+  else tc_gemm_kernel<BN><<<grid, NUM_THREADS, smem, st>>>(ma, mb, g);
   dl_note_launch();
   DL_CUDA(cudaGetLastError());
   return DL_OK;
@@ -555,9 +894,10 @@ extern "C" int dl_tc_gemm_ex(const float* A, const float* B, float* C, const flo
   }
   CUtensorMap ma, mb;
   // K-major: [MN rows, K cols], box = (tile rows) x 32 K;  MN-major: [K rows, MN cols], box = 32 K rows x 32 MN
-  int rc = a_mn ? make_map(&ma, A, K, M, lda, BK, true) : make_map(&ma, A, M, K, lda, BM, false);
+  // an MN-major A goes to TMEM through the converter threads in the TS kernel (no swizzle); the smem-operand kernel needs the UMMA layout
+  int rc = a_mn ? make_map(&ma, A, K, M, lda, BK, use_ts() ? 2 : 1) : make_map(&ma, A, M, K, lda, BM, 0);
   if (rc != DL_OK) return rc;
-  rc = b_mn ? make_map(&mb, B, K, N, ldb, BK, true) : make_map(&mb, B, N, K, ldb, bn, false);
+  rc = b_mn ? make_map(&mb, B, K, N, ldb, BK, 1) : make_map(&mb, B, N, K, ldb, bn, 0);
   if (rc != DL_OK) return rc;
   if (splits > 1 && !accumulate) {
     // split-K partial sums are added with atomics: start from zero (row by row: C may be a strided view)
@@ -608,12 +948,12 @@ extern "C" int dl_tc_conv5x5(int mode, const float* act, const float* w, float* 
   } else {
     g.M = Cout; g.N = kc; g.K = static_cast<int>(pixels); g.cA = 0;
     DL_REQUIRE(pixels % BK == 0, "dl_tc_conv5x5: wgrad needs B*H*W (%lld) to be a multiple of %d", pixels, BK);
-    rc = make_map(&ma, w, pixels, Cout, Cout, BK, true);                 // dY [pixels, Cout] as MN-major A
+    rc = make_map(&ma, w, pixels, Cout, Cout, BK, use_ts() ? 2 : 1);    // dY [pixels, Cout] as MN-major A
     if (rc != DL_OK) return rc;
   }
   const int bn = g.N <= 64 ? 64 : 128;
-  if (mode == 1) rc = make_map(&mb, w, Cout, kc, kc, bn, false);         // W K-major
-  else if (mode == 2) rc = make_map(&mb, w, Cout, kc, kc, BK, true);     // W MN-major: rows = cout (K), cols = (tap, cin)
+  if (mode == 1) rc = make_map(&mb, w, Cout, kc, kc, bn, 0);             // W K-major
+  else if (mode == 2) rc = make_map(&mb, w, Cout, kc, kc, BK, 1);        // W MN-major: rows = cout (K), cols = (tap, cin)
   else rc = make_map_nhwc(&mb, act, B, H, W, Cin, BK, true);             // X as MN-major B, 32-pixel boxes
   if (rc != DL_OK) return rc;
   g.ldc = g.N;
