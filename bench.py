@@ -33,7 +33,9 @@ def parse():
     p.add_argument("--impl", choices=["ours", "nccl", "reference"], default="ours")
     p.add_argument("--per-gpu-batch", type=int, default=128, help="examples/AsyncEASGD.sh:39 uses 128 per GPU")
     p.add_argument("--lr", type=float, default=0.1, help="examples/cifar10.lua:7")
-    p.add_argument("--graph", type=int, default=1, help="capture the step in a CUDA graph (ours)")
+    p.add_argument("--graph", type=int, default=None,
+                   help="capture the whole step in a CUDA graph (default: 1 for ours, 0 for nccl - the stock eager path; "
+                        "capturing NCCL inside the step graph hung on the 8-GPU box)")
     p.add_argument("--tf32", type=int, default=0, help="allow TF32 convolutions (default: strict fp32 like the reference)")
     p.add_argument("--variant", default="auto")
     p.add_argument("--nblocks", type=int, default=0)
@@ -45,7 +47,10 @@ def parse():
     p.add_argument("--bucket-mb", type=float, default=0.0,
                    help="ours: launch the fused kernel per gradient bucket of this size, overlapped with backward (0 = one launch)")
     p.add_argument("--bucket-blocks", type=int, default=32, help="CTAs per bucket launch (leaves the other SMs to cuDNN)")
-    return p.parse_args()
+    a = p.parse_args()
+    if a.graph is None:
+        a.graph = 1 if a.impl == "ours" else 0
+    return a
 
 
 def reference_arm(args) -> None:
