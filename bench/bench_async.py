@@ -53,7 +53,8 @@ def main():
         import torch_distlearn_b200 as dl
         comm = dl.P2PCommunicator(rank=rank, world=world, device=dev, heap_mb=96)
         flat = dl.FlatParams(comm, model)
-        algo = dl.AsyncEA(comm, "server" if rank == 0 else "client", args.tau, args.alpha, server_rank=0, num_clients=clients,
+        # tau = 1 inside the object: this script does the "every tau-th step" test itself so that both arms share it
+        algo = dl.AsyncEA(comm, "server" if rank == 0 else "client", 1, args.alpha, server_rank=0, num_clients=clients,
                           exclusive=bool(args.exclusive))
         if rank == 0:
             algo.initServer(flat)
@@ -123,8 +124,6 @@ def main():
                         n_sync += 1
             local_sgd(p, gr, None, lr=args.lr, zero_grads=True)
 
-        if args.impl == "ours":
-            algo.step = 0
         for i in range(args.tau):
             one_step(i, False)
         torch.cuda.synchronize()

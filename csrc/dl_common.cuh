@@ -27,7 +27,7 @@ struct DlPad {
 static_assert(sizeof(DlPad) % 16 == 0, "pad alignment");
 
 // Async-EASGD control block (lives in the server's pad; clients reach it over NVLink).
-#define DL_MAILBOX_WORDS 16
+#define DL_MAILBOX_WORDS 32
 struct DlAsyncCtl {
   unsigned int ticket_next;     // ticket lock: next ticket to hand out      (K11)
   unsigned int ticket_serving;  // ticket currently allowed in

@@ -52,7 +52,7 @@ struct HostPad {
   std::atomic<uint32_t> ticket_next;
   std::atomic<uint32_t> ticket_serving;
   std::atomic<uint64_t> sync_count;
-  std::atomic<uint64_t> mailbox[16];
+  std::atomic<uint64_t> mailbox[32];
 };
 static_assert(sizeof(HostPad) <= DL_PAD_BYTES, "host pad too large");
 
@@ -509,14 +509,14 @@ int dlh_async_sync_count(void* handle, int server, uint64_t* count) {
 
 int dlh_mailbox_write(void* handle, int rank, int index, uint64_t value) {
   Handle* h = static_cast<Handle*>(handle);
-  if (!h || rank < 0 || rank >= h->world || index < 0 || index >= 16) return DL_EINVAL;
+  if (!h || rank < 0 || rank >= h->world || index < 0 || index >= 32) return DL_EINVAL;
   h->pad(rank)->mailbox[index].store(value, std::memory_order_release);
   return DL_OK;
 }
 
 int dlh_mailbox_read(void* handle, int rank, int index, uint64_t* value) {
   Handle* h = static_cast<Handle*>(handle);
-  if (!h || rank < 0 || rank >= h->world || index < 0 || index >= 16 || !value) return DL_EINVAL;
+  if (!h || rank < 0 || rank >= h->world || index < 0 || index >= 32 || !value) return DL_EINVAL;
   *value = h->pad(rank)->mailbox[index].load(std::memory_order_acquire);
   return DL_OK;
 }

@@ -155,7 +155,7 @@ int dl_peer_pull(const dl_comm_t* c, int src_rank, uint64_t off, float* dst, uin
 /* Read the server's sync counter (number of completed client syncs). */
 int dl_async_sync_count(const dl_comm_t* c, int server, uint64_t* count, void* stream);
 
-/* Host-visible 64-bit mailbox words in rank `rank`'s pad (index < 16): the tester handshake
+/* Host-visible 64-bit mailbox words in rank `rank`'s pad (index < 32): the tester handshake
  * "Test?"/"Ack" (lua/AsyncEA.lua:239-258,268-292) and ready/done flags travel here. */
 int dl_mailbox_write(const dl_comm_t* c, int rank, int index, uint64_t value, void* stream);
 int dl_mailbox_read(const dl_comm_t* c, int rank, int index, uint64_t* value, void* stream);

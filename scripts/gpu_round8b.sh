@@ -7,6 +7,9 @@ timeout 90 $TR --master-port 29545 bench.py --gpus 8 --steps 100 --warmup 10 --i
 for impl in ours nccl; do
 timeout 90 $TR --master-port 29546 bench/bench_ea.py --impl $impl --batch 1 --steps 1000 > gpurun_out/ea8_$impl.log 2>&1; echo "ea $impl rc=$?"; tail -n 1 gpurun_out/ea8_$impl.log | cut -c1-300
 done
+for impl in ours nccl; do
+timeout 90 $TR --master-port 29548 bench/bench_ea.py --impl $impl --batch 64 --tau 1 --steps 500 > gpurun_out/ea8_tau1_$impl.log 2>&1; echo "ea tau1 $impl rc=$?"; tail -n 1 gpurun_out/ea8_tau1_$impl.log | cut -c1-300
+done
 for impl in ours hostloop; do
 timeout 120 $TR --master-port 29547 bench/bench_async.py --impl $impl --steps 100 > gpurun_out/async8_$impl.log 2>&1; echo "async $impl rc=$?"; tail -n 1 gpurun_out/async8_$impl.log | cut -c1-400
 done

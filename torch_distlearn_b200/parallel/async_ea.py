@@ -40,7 +40,8 @@ from .flat import FlatParams, TableStager, walk_table
 
 # mailbox words in the SERVER's pad
 MB_READY, MB_TEST_SEQ, MB_TEST_ACK, MB_STOP = 0, 1, 2, 3
-MB_DONE_BASE = 8  # words 8..15: rank r sets word 8+r when it has finished training
+MB_DONE_BASE = 8     # words 8..15: rank r sets word 8+r when it has finished training
+MB_PULLED_BASE = 16  # words 16..23: rank r sets word 16+r once it has pulled the initial center
 
 
 class AsyncEA:
@@ -170,6 +171,15 @@ class AsyncEA:
         self.comm.peer_pull(self.server_rank, self._center, self._x, self._n)
         self._unpack()
         self.comm.synchronize()
+        # The reference's initServer hands the same center to EVERY client before the first sync can happen
+        # (lua/AsyncEA.lua:155-159).  Syncs need no server here, so the clients gate themselves: nobody starts
+        # training (and moving the center) until all of them have taken their copy of the initial one.
+        self.comm.mailbox_write(self.server_rank, MB_PULLED_BASE + self.comm.rank, 1)
+        if self.num_clients is not None:
+            def all_pulled():
+                return sum(1 for r in range(self.comm.world)
+                           if self.comm.mailbox_read(self.server_rank, MB_PULLED_BASE + r) == 1) >= self.num_clients
+            self._wait(all_pulled, timeout, "every client to pull the initial center")
 
     def syncClient(self, params: Any = None) -> bool:
         """Call once per local step; every ``tau``-th call does the elastic exchange with the center
