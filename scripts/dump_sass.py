@@ -14,6 +14,8 @@ WANT = {
     "fused_ea_kernelILi8ELb0ELb0E": "fused_ea_twoshot_w8", "allreduce_twoshot_kernelILi8ELb1ELb0E": "allreduce_nvls_w8",
     "async_ea_client_kernel": "async_ea_client", "broadcast_kernelILi2ELb0E": "broadcast_nvls",
     "sgd_twoshot_kernelILi1ELb0ELb0E": "fused_sgd_w1",
+    "tc_gemm_ts_kernelILi128E": "tc_gemm_ts_bn128", "tc_gemm_kernelILi128E": "tc_gemm_smemA_bn128",
+    "bn_relu_pool_bwd_apply_kernel": "bn_relu_pool_bwd_apply", "bn_stats_kernel": "bn_stats",
 }
 KEYS = ("LD.E", "ST.E", "LDL", "STL", "LDGMC", "REDG", "RED.", "STG", "LDG", "ATOM", "MEMBAR", "CCTL", "ERRBAR", "UTC", "LDTM", "STTM", "UTMA", "UBLKCP", "SYNCS")
 
@@ -33,12 +35,12 @@ def main():
                 open(os.path.join(OUT, out + ".sass"), "w").write("Function : " + f)
                 summary.append((out, dem, key))
     with open(os.path.join(OUT, "README.md"), "w") as fh:
-        fh.write("# SASS listings of the collective kernels (`cuobjdump -sass libdistlearn_b200.so`, sm_100a)\n\n"
+        fh.write("# SASS listings of the collective and tensor-core kernels (`cuobjdump -sass libdistlearn_b200.so`, sm_100a)\n\n"
                  "Regenerate with `python scripts/dump_sass.py`.  Memory instructions per kernel (opcode: static count).\n"
                  "`LDGMC.E.ADD.F32x4...` = `multimem.ld_reduce` (in-switch reduction); `STG.E.128.STRONG.SYS` on the multicast\n"
                  "mapping = `multimem.st`; `REDG.E.ADD.F32x4...SYS` = vector atomics over NVLink; `LDG.E.NA.128` / `STG.E.NA.128`\n"
                  "(`L1::no_allocate`) on peer-mapped pointers = P2P loads/stores; `LDG/STG.E.64.STRONG.SYS` + `MEMBAR.ALL.SYS` +\n"
-                 "`CCTL.IVALL` = the release/acquire flags of the signal pad; `LD.E.128`/`ST.E.128` = generic-address accesses to the local\nheap (parameters, momentum); `LDL/STL` = the stack copy of `dl_comm_t.base[]` that dynamic rank indexing needs.\n\n")
+                 "`CCTL.IVALL` = the release/acquire flags of the signal pad; `UTCHMMA` = `tcgen05.mma`, `UTMALDG` = TMA tensor loads, `LDTM`/`STTM` = `tcgen05.ld`/`tcgen05.st` (tensor memory),\n`UTCBAR` = `tcgen05.commit`, `SYNCS.*` = mbarrier operations; `LD.E.128`/`ST.E.128` = generic-address accesses to the local\nheap (parameters, momentum); `LDL/STL` = the stack copy of `dl_comm_t.base[]` that dynamic rank indexing needs.\n\n")
         for out, dem, key in sorted(summary):
             fh.write(f"## {out}.sass\n`{dem}`\n\n")
             for o, c in sorted(key.items()):
