@@ -134,7 +134,8 @@ __device__ __forceinline__ float4 operator+(const float4& a, const float4& b) {
   return make_float4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w);
 }
 __device__ __forceinline__ float4 dl_scale(const float4& a, float s) {
-  return make_float4(a.x * s, a.y * s, a.z * s, a.w * s);
+  // __fmul_rn: never fused into a following add (the result must not depend on which kernel inlined this)
+  return make_float4(__fmul_rn(a.x, s), __fmul_rn(a.y, s), __fmul_rn(a.z, s), __fmul_rn(a.w, s));
 }
 
 // ---- the block-level cross-rank barrier ---------------------------------------------------

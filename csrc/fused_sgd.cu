@@ -28,23 +28,25 @@ struct SgdArgs {
   int channel;
 };
 
+// The update rule with its rounding pinned down (explicit fmaf, no compiler-chosen contraction): every variant of
+// the kernel — one-shot, two-shot, NVLS, any bucket geometry — then produces the same bits from the same sums.
+__device__ __forceinline__ float sgd_update1(float g, float p, float* m, const SgdArgs& a) {
+  if (a.wd != 0.f) g = fmaf(a.wd, p, g);
+  if (m != nullptr) {
+    const float mv = fmaf(a.momentum, *m, g);
+    *m = mv;
+    g = a.nesterov ? fmaf(a.momentum, mv, g) : mv;
+  }
+  return fmaf(-a.lr, g, p);
+}
 __device__ __forceinline__ float4 sgd_update(float4 g, float4 p, float4* m_ptr, const SgdArgs& a) {
-  if (a.wd != 0.f) {
-    g.x += a.wd * p.x; g.y += a.wd * p.y; g.z += a.wd * p.z; g.w += a.wd * p.w;
-  }
-  if (m_ptr != nullptr) {
-    float4 m = *m_ptr;
-    m.x = a.momentum * m.x + g.x; m.y = a.momentum * m.y + g.y;
-    m.z = a.momentum * m.z + g.z; m.w = a.momentum * m.w + g.w;
-    *m_ptr = m;
-    if (a.nesterov) {
-      g.x += a.momentum * m.x; g.y += a.momentum * m.y; g.z += a.momentum * m.z; g.w += a.momentum * m.w;
-    } else {
-      g = m;
-    }
-  }
-  p.x -= a.lr * g.x; p.y -= a.lr * g.y; p.z -= a.lr * g.z; p.w -= a.lr * g.w;
-  return p;
+  float* m = reinterpret_cast<float*>(m_ptr);
+  float4 r;
+  r.x = sgd_update1(g.x, p.x, m ? m + 0 : nullptr, a);
+  r.y = sgd_update1(g.y, p.y, m ? m + 1 : nullptr, a);
+  r.z = sgd_update1(g.z, p.z, m ? m + 2 : nullptr, a);
+  r.w = sgd_update1(g.w, p.w, m ? m + 3 : nullptr, a);
+  return r;
 }
 
 // One pass over the owner's slice [s.begin, s.end): reduce the gradients of the active ranks
@@ -238,15 +240,7 @@ __global__ void __launch_bounds__(DL_THREADS) local_sgd_kernel(LocalSgdArgs a) {
   // scalar tail (n not a multiple of 4)
   for (unsigned long long i = n4 * 4 + static_cast<unsigned long long>(blockIdx.x) * DL_THREADS + threadIdx.x;
        i < a.n; i += stride) {
-    float g = a.g[i] * a.scale;
-    float p = a.p[i];
-    if (a.wd != 0.f) g += a.wd * p;
-    if (a.m) {
-      float m = a.momentum * a.m[i] + g;
-      a.m[i] = m;
-      g = a.nesterov ? g + a.momentum * m : m;
-    }
-    a.p[i] = p - a.lr * g;
+    a.p[i] = sgd_update1(__fmul_rn(a.g[i], a.scale), a.p[i], a.m ? a.m + i : nullptr, s);
     if (a.zero_grads) a.g[i] = 0.f;
   }
 }
