@@ -50,16 +50,32 @@ __global__ void __launch_bounds__(BN_THREADS) bn_stats_kernel(const float4* __re
   }
 }
 
+// Finalize kernels: block = 32 channels x 16 slices.  Slice y adds the partial rows y, y+16, ... of its channel in
+// double, the 16 slice sums meet in shared memory and thread y == 0 adds them in a fixed order (deterministic).  One
+// thread per channel walking all ~300 partial rows alone took 20-40 us per call; this takes a few.
+#define FIN_X 32
+#define FIN_Y 16
+__device__ __forceinline__ double fin_sum(const float* partial, int nblocks, long long row_stride, int c, double (*sh)[FIN_X]) {
+  double a = 0.0;
+  for (int b = threadIdx.y; b < nblocks; b += FIN_Y) a += static_cast<double>(partial[static_cast<long long>(b) * row_stride + c]);
+  sh[threadIdx.y][threadIdx.x] = a;
+  __syncthreads();
+  double t = 0.0;
+  if (threadIdx.y == 0)
+    for (int k = 0; k < FIN_Y; ++k) t += sh[k][threadIdx.x];
+  __syncthreads();
+  return t;
+}
+
 // mean / invstd from the sums; running statistics like nn.BatchNorm2d (momentum, unbiased variance)
 __global__ void bn_finalize_kernel(const float* partial, int nblocks, long long M, int C, float eps, float momentum,
                                    float* mean, float* invstd, float* running_mean, float* running_var) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= C) return;
-  double sum = 0.0, sumsq = 0.0;
-  for (int b = 0; b < nblocks; ++b) {
-    sum += static_cast<double>(partial[(static_cast<long long>(b) * 2 + 0) * C + c]);
-    sumsq += static_cast<double>(partial[(static_cast<long long>(b) * 2 + 1) * C + c]);
-  }
+  __shared__ double sh[FIN_Y][FIN_X];
+  const int c = blockIdx.x * FIN_X + threadIdx.x;           // C is a multiple of 4; channels >= C read channel C-1 and are dropped
+  const int cc = c < C ? c : C - 1;
+  const double sum = fin_sum(partial, nblocks, 2LL * C, cc, sh);
+  const double sumsq = fin_sum(partial + C, nblocks, 2LL * C, cc, sh);
+  if (c >= C || threadIdx.y != 0) return;
   const double m = sum / static_cast<double>(M);
   double var = sumsq / static_cast<double>(M) - m * m;
   if (var < 0) var = 0;
@@ -186,13 +202,12 @@ __global__ void __launch_bounds__(BN_THREADS) bn_relu_pool_bwd_reduce_kernel(con
 
 // sums of the per-block partials of the backward reduction -> sum_dz, sum_dzx (double), dgamma, dbeta
 __global__ void bn_bwd_finalize_kernel(const float* partial, int nblocks, int C, double* sums, float* dgamma, float* dbeta) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= C) return;
-  double a = 0.0, b = 0.0;
-  for (int k = 0; k < nblocks; ++k) {
-    a += static_cast<double>(partial[(static_cast<long long>(k) * 2 + 0) * C + c]);
-    b += static_cast<double>(partial[(static_cast<long long>(k) * 2 + 1) * C + c]);
-  }
+  __shared__ double sh[FIN_Y][FIN_X];
+  const int c = blockIdx.x * FIN_X + threadIdx.x;
+  const int cc = c < C ? c : C - 1;
+  const double a = fin_sum(partial, nblocks, 2LL * C, cc, sh);
+  const double b = fin_sum(partial + C, nblocks, 2LL * C, cc, sh);
+  if (c >= C || threadIdx.y != 0) return;
   sums[c] = a;
   sums[C + c] = b;
   dbeta[c] = static_cast<float>(a);
@@ -291,7 +306,7 @@ extern "C" int dl_bn_relu_pool_fwd(const float* y, float* p, const float* gamma,
                                                                          reinterpret_cast<float4*>(partial));
   dl_note_launch();
   DL_CUDA(cudaGetLastError());
-  bn_finalize_kernel<<<(C + 127) / 128, 128, 0, st>>>(partial, nb, M, C, eps, momentum, mean, invstd, running_mean, running_var);
+  bn_finalize_kernel<<<(C + FIN_X - 1) / FIN_X, dim3(FIN_X, FIN_Y), 0, st>>>(partial, nb, M, C, eps, momentum, mean, invstd, running_mean, running_var);
   dl_note_launch();
   DL_CUDA(cudaGetLastError());
   const long long items = M / 4 * C4;
@@ -323,7 +338,7 @@ extern "C" int dl_bn_relu_pool_bwd(const float* y, const float* dp, float* dy, c
       reinterpret_cast<float4*>(partial));
   dl_note_launch();
   DL_CUDA(cudaGetLastError());
-  bn_bwd_finalize_kernel<<<(C + 127) / 128, 128, 0, st>>>(partial, nb, C, sums, dgamma, dbeta);
+  bn_bwd_finalize_kernel<<<(C + FIN_X - 1) / FIN_X, dim3(FIN_X, FIN_Y), 0, st>>>(partial, nb, C, sums, dgamma, dbeta);
   dl_note_launch();
   DL_CUDA(cudaGetLastError());
   bn_relu_pool_bwd_apply_kernel<<<bn_grid(windows * C4, BN_THREADS), BN_THREADS, 0, st>>>(
@@ -362,10 +377,11 @@ __global__ void __launch_bounds__(BN_THREADS) colsum_kernel(const float4* __rest
 }
 
 __global__ void colsum_finalize_kernel(const float* partial, int nblocks, int C, float* out) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= C) return;
-  double a = 0.0;
-  for (int k = 0; k < nblocks; ++k) a += static_cast<double>(partial[static_cast<long long>(k) * C + c]);
+  __shared__ double sh[FIN_Y][FIN_X];
+  const int c = blockIdx.x * FIN_X + threadIdx.x;
+  const int cc = c < C ? c : C - 1;
+  const double a = fin_sum(partial, nblocks, C, cc, sh);
+  if (c >= C || threadIdx.y != 0) return;
   out[c] = static_cast<float>(a);
 }
 
@@ -381,7 +397,7 @@ extern "C" int dl_colsum(const float* x, float* out, long long M, int C, void* w
                                                                    reinterpret_cast<float4*>(work));
   dl_note_launch();
   DL_CUDA(cudaGetLastError());
-  colsum_finalize_kernel<<<(C + 127) / 128, 128, 0, st>>>(static_cast<const float*>(work), nb, C, out);
+  colsum_finalize_kernel<<<(C + FIN_X - 1) / FIN_X, dim3(FIN_X, FIN_Y), 0, st>>>(static_cast<const float*>(work), nb, C, out);
   dl_note_launch();
   DL_CUDA(cudaGetLastError());
   return DL_OK;

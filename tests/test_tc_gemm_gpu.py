@@ -90,7 +90,7 @@ def _conv_case(B, cin, cout, H, seed=0):
 
 
 @pytest.mark.parametrize("implicit", [False, True])
-@pytest.mark.parametrize("B,cin,cout,H", [(4, 3, 64, 32), (8, 64, 128, 16), (6, 128, 256, 8), (4, 256, 512, 4), (128, 64, 128, 16)])
+@pytest.mark.parametrize("B,cin,cout,H", [(4, 3, 64, 32), (8, 64, 128, 16), (6, 128, 256, 8), (4, 256, 512, 4), (128, 64, 128, 16), (1, 32, 32, 16), (2, 32, 96, 8)])
 def test_conv5x5_forward_backward_vs_float64_conv2d(B, cin, cout, H, implicit):
     """Explicit (im2col + GEMM + col2im) and implicit (4-D TMA halo boxes) paths against float64 conv2d."""
     from torch_distlearn_b200.ops import TCConv5x5

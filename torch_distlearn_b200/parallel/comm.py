@@ -30,6 +30,7 @@ import torch
 from .. import _lib
 from .._lib import DL_PAD_BYTES, DlComm, DlResult, VARIANT_NAMES, VARIANT_NVLS, VARIANT_ONESHOT, VARIANT_TWOSHOT
 
+VARIANT_TEXT = {VARIANT_ONESHOT: "oneshot", VARIANT_TWOSHOT: "twoshot", VARIANT_NVLS: "nvls"}
 _ALIGN = 512  # byte alignment of every symmetric allocation (>= 16 for 128-bit access)
 
 _DTYPE_CODES = {torch.float32: _lib.DT_F32, torch.int32: _lib.DT_I32, torch.int64: _lib.DT_I64,
@@ -277,6 +278,25 @@ class _CudaMem:
                                          "strides": None}
 
 
+_NVTX = os.environ.get("DL_B200_NVTX", "0") == "1"
+
+
+class _Range:
+    """NVTX range around a collective launch when DL_B200_NVTX=1 (the reference has no tracing at all, SURVEY §5);
+    shows up in Nsight Systems timelines next to the kernel names."""
+
+    def __init__(self, name: str):
+        self.name = name
+
+    def __enter__(self):
+        if _NVTX:
+            torch.cuda.nvtx.range_push(self.name)
+
+    def __exit__(self, *exc):
+        if _NVTX:
+            torch.cuda.nvtx.range_pop()
+
+
 def _stream_ptr(device: torch.device, stream: Optional[torch.cuda.Stream] = None) -> int:
     s = stream if stream is not None else torch.cuda.current_stream(device)
     return s.cuda_stream
@@ -313,7 +333,7 @@ class _CudaOps(Communicator):
         v = self.pick_variant("allreduce", nbytes, variant)
         if buf.dtype != torch.float32 and v != VARIANT_ONESHOT:
             v = VARIANT_ONESHOT
-        with torch.cuda.device(self.device):
+        with torch.cuda.device(self.device), _Range(f"distlearn.allreduce[{VARIANT_TEXT[v]}]"):
             _lib.check(self._lib.dl_allreduce(C.byref(self._c), _DTYPE_CODES[buf.dtype], buf.offset, n, v, int(active),
                                               int(payload), int(normalize), self._nb(nblocks), channel,
                                               _stream_ptr(self.device, stream)))
@@ -325,7 +345,7 @@ class _CudaOps(Communicator):
                   payload: int = 0, zero_grads: bool = True, variant: str = "auto", channel: int = 0, read: bool = False,
                   nblocks: int = 0, stream=None):
         v = self.pick_variant("fused_sgd", n * 4, variant)
-        with torch.cuda.device(self.device):
+        with torch.cuda.device(self.device), _Range(f"distlearn.fused_sgd[{VARIANT_TEXT[v]}]"):
             _lib.check(self._lib.dl_fused_sgd(C.byref(self._c), grads.offset, params.offset,
                                               momentum_buf.offset if momentum_buf else 0, n, lr, momentum, weight_decay,
                                               int(nesterov), v, int(active), int(payload), int(zero_grads),
@@ -337,7 +357,7 @@ class _CudaOps(Communicator):
                  payload: int = 0, variant: str = "auto", channel: int = 0, read: bool = False, nblocks: int = 0,
                  stream=None):
         v = self.pick_variant("fused_ea", n * 4, variant)
-        with torch.cuda.device(self.device):
+        with torch.cuda.device(self.device), _Range(f"distlearn.fused_ea[{VARIANT_TEXT[v]}]"):
             _lib.check(self._lib.dl_fused_ea(C.byref(self._c), x.offset, c_cur.offset, c_next.offset, n, alpha, v,
                                              int(active), int(payload), self._nb(nblocks), channel,
                                              _stream_ptr(self.device, stream)))
@@ -349,7 +369,7 @@ class _CudaOps(Communicator):
                   stream=None):
         n = buf.numel if n is None else n
         v = self.pick_variant("broadcast", n * 4, variant)
-        with torch.cuda.device(self.device):
+        with torch.cuda.device(self.device), _Range(f"distlearn.broadcast[{VARIANT_TEXT[v]}]"):
             _lib.check(self._lib.dl_broadcast(C.byref(self._c), buf.offset, also.offset if also else 0, n, root, v,
                                               int(payload), self._nb(nblocks), channel, _stream_ptr(self.device, stream)))
             self.launches += 1
