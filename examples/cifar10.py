@@ -18,7 +18,7 @@ import torch
 
 import torch_distlearn_b200 as dl
 from torch_distlearn_b200.launch import shutdown
-from torch_distlearn_b200.models import cifar_convnet
+from torch_distlearn_b200.models import cifar_convnet, cifar_convnet_tc
 from torch_distlearn_b200.parallel.trainer import TrainStep
 from torch_distlearn_b200.utils import ConfusionMatrix, Data
 from torch_distlearn_b200.utils.config import base_parser
@@ -28,12 +28,16 @@ def main(argv=None):
     p = base_parser("CIFAR-10 AllReduceSGD (examples/cifar10.lua)", batch_size=32, learning_rate=0.1)
     p.add_argument("--graph", action="store_true", help="capture the whole step in a CUDA graph (needs equal step counts)")
     p.add_argument("--bucketMB", type=float, default=0.0, help="overlap per-bucket fused launches with backward")
+    p.add_argument("--conv", choices=["auto", "tc", "cudnn"], default="auto",
+                   help="tc = convolutions as implicit GEMMs on the tensor cores (3xTF32, fp32-level accuracy; CUDA only), "
+                        "cudnn = stock torch modules; auto = tc with --cuda")
     opt = p.parse_args(argv)
     comm, log = setup(opt)
     dev = comm.device
     batch = math.ceil(opt.batchSize / opt.numNodes)                 # examples/cifar10.lua:36
     data = Data(opt.nodeIndex, opt.numNodes, batch, device=dev, train_samples=opt.trainSamples, test_samples=opt.testSamples)
-    model = cifar_convnet(seed=opt.seed).to(dev)
+    use_tc = dev.type == "cuda" and opt.conv in ("auto", "tc")
+    model = (cifar_convnet_tc(seed=opt.seed) if use_tc else cifar_convnet(seed=opt.seed)).to(dev)
     flat = dl.FlatParams(comm, model, with_momentum=opt.momentum != 0)
     sgd = dl.AllReduceSGD(comm, flat)
     if opt.resume:
