@@ -79,3 +79,34 @@ def test_vmm_alloc_export_import_map_and_torch_alias():
     _lib.check(lib.dl_vmm_unmap(p1.value, nbytes))
     _lib.check(lib.dl_vmm_release(handle.value))
     lib.dl_close_fd(fd.value)
+
+
+def test_checkpoint_round_trip_on_cpu(tmp_path):
+    """Flat params + center + momentum checkpoint (utils/checkpoint.py) with a CPU communicator: header fields,
+    shape manifest, in-place load that keeps the parameter views valid, mismatch detection."""
+    import uuid
+    import torch_distlearn_b200 as dl
+    comm = dl.HostCommunicator(0, 1, name=f"ck-{uuid.uuid4().hex[:8]}", heap_mb=4)
+    try:
+        model = torch.nn.Sequential(torch.nn.Linear(5, 7), torch.nn.Linear(7, 3))
+        flat = dl.FlatParams(comm, model, with_momentum=True)
+        center = comm.alloc(flat.padded, torch.float32, "center")
+        center.tensor.copy_(flat.params.tensor * 2)
+        flat.momentum.tensor.fill_(0.25)
+        path = str(tmp_path / "m.dlb200")
+        dl.save_checkpoint(path, flat, center=center, momentum=flat.momentum, algo="AllReduceEA", tau=3, alpha=0.4, step=9,
+                           world=4, extra={"epoch": 2})
+        want_p, want_c = flat.params.tensor.clone(), center.tensor.clone()
+        weight_view = model[0].weight
+        flat.params.tensor.zero_(); center.tensor.zero_(); flat.momentum.tensor.zero_()
+        hdr = dl.load_checkpoint(path, flat, center=center, momentum=flat.momentum)
+        assert (hdr["algo"], hdr["tau"], hdr["step"], hdr["world"], hdr["extra"]["epoch"]) == ("AllReduceEA", 3, 9, 4, 2)
+        assert [m["name"] for m in hdr["manifest"]] == ["0.weight", "0.bias", "1.weight", "1.bias"]
+        assert torch.equal(flat.params.tensor, want_p) and torch.equal(center.tensor, want_c)
+        assert float(flat.momentum.tensor[0]) == 0.25
+        assert weight_view.data_ptr() == model[0].weight.data_ptr() and torch.equal(model[0].weight.flatten(), want_p[:35])
+        other = dl.FlatParams(comm, torch.nn.Linear(4, 4))
+        with pytest.raises(ValueError):
+            dl.load_checkpoint(path, other)
+    finally:
+        comm.close()
