@@ -201,7 +201,8 @@ __global__ void __launch_bounds__(BN_THREADS) bn_relu_pool_bwd_reduce_kernel(con
 }
 
 // sums of the per-block partials of the backward reduction -> sum_dz, sum_dzx (double), dgamma, dbeta
-__global__ void bn_bwd_finalize_kernel(const float* partial, int nblocks, int C, double* sums, float* dgamma, float* dbeta) {
+__global__ void bn_bwd_finalize_kernel(const float* partial, int nblocks, int C, double* sums, float* dgamma, float* dbeta,
+                                       int accumulate) {
   __shared__ double sh[FIN_Y][FIN_X];
   const int c = blockIdx.x * FIN_X + threadIdx.x;
   const int cc = c < C ? c : C - 1;
@@ -210,8 +211,9 @@ __global__ void bn_bwd_finalize_kernel(const float* partial, int nblocks, int C,
   if (c >= C || threadIdx.y != 0) return;
   sums[c] = a;
   sums[C + c] = b;
-  dbeta[c] = static_cast<float>(a);
-  dgamma[c] = static_cast<float>(b);
+  // accumulate: add into the caller's gradient buffers (the parameters' .grad) instead of overwriting them
+  dbeta[c] = (accumulate ? dbeta[c] : 0.f) + static_cast<float>(a);
+  dgamma[c] = (accumulate ? dgamma[c] : 0.f) + static_cast<float>(b);
 }
 
 // ---- backward apply: dy for the four positions of each window ----------------------------------------
@@ -321,7 +323,7 @@ extern "C" int dl_bn_relu_pool_fwd(const float* y, float* p, const float* gamma,
 // dp [B,H/2,W/2,C] -> dy [B,H,W,C], dgamma [C], dbeta [C]; y, mean, invstd as saved by the forward call.
 extern "C" int dl_bn_relu_pool_bwd(const float* y, const float* dp, float* dy, const float* gamma, const float* beta,
                                    const float* mean, const float* invstd, float* dgamma, float* dbeta, int B, int H, int W, int C,
-                                   void* work, void* stream) {
+                                   int accumulate, void* work, void* stream) {
   DL_REQUIRE(y && dp && dy && gamma && beta && mean && invstd && dgamma && dbeta && work, "dl_bn_relu_pool_bwd: null pointer");
   DL_REQUIRE(C % 4 == 0 && C / 4 <= BN_THREADS && H % 2 == 0 && W % 2 == 0, "dl_bn_relu_pool_bwd: need C %% 4 == 0, C <= %d, even H and W",
              BN_THREADS * 4);
@@ -338,7 +340,7 @@ extern "C" int dl_bn_relu_pool_bwd(const float* y, const float* dp, float* dy, c
       reinterpret_cast<float4*>(partial));
   dl_note_launch();
   DL_CUDA(cudaGetLastError());
-  bn_bwd_finalize_kernel<<<(C + FIN_X - 1) / FIN_X, dim3(FIN_X, FIN_Y), 0, st>>>(partial, nb, C, sums, dgamma, dbeta);
+  bn_bwd_finalize_kernel<<<(C + FIN_X - 1) / FIN_X, dim3(FIN_X, FIN_Y), 0, st>>>(partial, nb, C, sums, dgamma, dbeta, accumulate);
   dl_note_launch();
   DL_CUDA(cudaGetLastError());
   bn_relu_pool_bwd_apply_kernel<<<bn_grid(windows * C4, BN_THREADS), BN_THREADS, 0, st>>>(
@@ -376,16 +378,16 @@ __global__ void __launch_bounds__(BN_THREADS) colsum_kernel(const float4* __rest
   }
 }
 
-__global__ void colsum_finalize_kernel(const float* partial, int nblocks, int C, float* out) {
+__global__ void colsum_finalize_kernel(const float* partial, int nblocks, int C, float* out, int accumulate) {
   __shared__ double sh[FIN_Y][FIN_X];
   const int c = blockIdx.x * FIN_X + threadIdx.x;
   const int cc = c < C ? c : C - 1;
   const double a = fin_sum(partial, nblocks, C, cc, sh);
   if (c >= C || threadIdx.y != 0) return;
-  out[c] = static_cast<float>(a);
+  out[c] = (accumulate ? out[c] : 0.f) + static_cast<float>(a);
 }
 
-extern "C" int dl_colsum(const float* x, float* out, long long M, int C, void* work, void* stream) {
+extern "C" int dl_colsum(const float* x, float* out, long long M, int C, int accumulate, void* work, void* stream) {
   DL_REQUIRE(x && out && work && M > 0, "dl_colsum: bad arguments");
   DL_REQUIRE(C % 4 == 0 && C / 4 <= BN_THREADS, "dl_colsum: need C %% 4 == 0 and C <= %d", BN_THREADS * 4);
   DL_REQUIRE(reinterpret_cast<uintptr_t>(x) % 16 == 0 && reinterpret_cast<uintptr_t>(work) % 16 == 0, "dl_colsum: 16-byte alignment required");
@@ -397,7 +399,7 @@ extern "C" int dl_colsum(const float* x, float* out, long long M, int C, void* w
                                                                    reinterpret_cast<float4*>(work));
   dl_note_launch();
   DL_CUDA(cudaGetLastError());
-  colsum_finalize_kernel<<<(C + FIN_X - 1) / FIN_X, dim3(FIN_X, FIN_Y), 0, st>>>(static_cast<const float*>(work), nb, C, out);
+  colsum_finalize_kernel<<<(C + FIN_X - 1) / FIN_X, dim3(FIN_X, FIN_Y), 0, st>>>(static_cast<const float*>(work), nb, C, out, accumulate);
   dl_note_launch();
   DL_CUDA(cudaGetLastError());
   return DL_OK;

@@ -201,9 +201,12 @@ int dl_bn_relu_pool_fwd(const float* y, float* p, const float* gamma, const floa
                         float* running_mean, float* running_var, int B, int H, int W, int C, float eps, float momentum,
                         void* work, void* stream);
 int dl_bn_relu_pool_bwd(const float* y, const float* dp, float* dy, const float* gamma, const float* beta, const float* mean,
-                        const float* invstd, float* dgamma, float* dbeta, int B, int H, int W, int C, void* work, void* stream);
-/* out[C] = column sums of x[M, C] (a convolution's bias gradient); work: dl_bn_work_bytes(C) bytes. */
-int dl_colsum(const float* x, float* out, long long M, int C, void* work, void* stream);
+                        const float* invstd, float* dgamma, float* dbeta, int B, int H, int W, int C, int accumulate,
+                        void* work, void* stream);
+/* out[C] (+)= column sums of x[M, C] (a convolution's bias gradient); work: dl_bn_work_bytes(C) bytes.
+ * accumulate != 0 (here and in dl_bn_relu_pool_bwd for dgamma/dbeta) adds into the buffer: the autograd functions
+ * pass the parameters' .grad views so that no separate gradient-accumulation kernel runs. */
+int dl_colsum(const float* x, float* out, long long M, int C, int accumulate, void* work, void* stream);
 
 /* ---- local flat-vector ops (single GPU, no communication) ---- */
 /* p -= lr * (g*scale [+ wd*p] [momentum]); optionally zero g. world==1 fast path. */

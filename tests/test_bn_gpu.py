@@ -34,6 +34,13 @@ def test_fused_bn_relu_pool_matches_float64(B, H, C):
     close(y1.grad, y64.grad, 5e-5)
     close(mod.weight.grad, ref.weight.grad, 5e-5)
     close(mod.bias.grad, ref.bias.grad, 5e-5)
+    # a second backward accumulates into the existing .grad inside the kernel: exactly twice the first
+    g1, b1 = mod.weight.grad.clone(), mod.bias.grad.clone()
+    rm, rv = mod.running_mean.clone(), mod.running_var.clone()
+    mod(y.clone().requires_grad_(True)).backward(dp)
+    torch.testing.assert_close(mod.weight.grad, 2 * g1, rtol=1e-5, atol=1e-5)
+    torch.testing.assert_close(mod.bias.grad, 2 * b1, rtol=1e-5, atol=1e-5)
+    mod.running_mean.copy_(rm); mod.running_var.copy_(rv)
     close(mod.running_mean, ref.running_mean, 1e-5)
     close(mod.running_var, ref.running_var, 1e-5)
     # eval mode uses the running statistics through the plain torch path

@@ -121,6 +121,12 @@ def test_conv5x5_forward_backward_vs_float64_conv2d(B, cin, cout, H, implicit):
     assert rel(x_nhwc.grad.permute(0, 3, 1, 2), x64.grad) < 1e-5
     assert rel(tc.weight.grad.view(cout, 5, 5, cin).permute(0, 3, 1, 2), conv64.weight.grad) < 1e-5
     assert rel(tc.bias.grad, conv64.bias.grad) < 1e-5
+    # second backward: .grad exists now, so the backward kernels add into it themselves (ops.bn.grad_sink) —
+    # the result must be what autograd's own accumulation would give: twice the first gradient
+    w1, b1 = tc.weight.grad.clone(), tc.bias.grad.clone()
+    tc(x_nhwc.detach().requires_grad_(True)).backward(dy.permute(0, 2, 3, 1).contiguous())
+    torch.testing.assert_close(tc.weight.grad, 2 * w1, rtol=1e-5, atol=1e-6 * float(w1.abs().max()))
+    torch.testing.assert_close(tc.bias.grad, 2 * b1, rtol=1e-5, atol=1e-6 * float(b1.abs().max()) + 1e-6)
 
 
 def test_tc_model_matches_reference_model():

@@ -13,16 +13,43 @@ def _stream(t: torch.Tensor) -> int:
     return torch.cuda.current_stream(t.device).cuda_stream
 
 
-def colsum(x: torch.Tensor) -> torch.Tensor:
-    """Column sums of a contiguous [M, C] fp32 CUDA matrix (C % 4 == 0): the bias gradient of a convolution."""
+def grad_sink(p) -> "torch.Tensor | None":
+    """The tensor a backward kernel may accumulate a parameter gradient into directly, or None.
+
+    Autograd adds a returned gradient into ``p.grad`` with one extra element-wise kernel per parameter; the
+    backward kernels of this package can add into ``p.grad`` themselves (it is a view of the flat gradient vector,
+    zeroed by the fused SGD kernel).  That is only done when it is indistinguishable from autograd's accumulation:
+    ``p.grad`` exists, is dense fp32 of the parameter's shape, and nobody listens for the accumulation event
+    (post-accumulate hooks, e.g. GradBuckets, still get the ordinary path)."""
+    if not DIRECT_GRAD or not isinstance(p, torch.nn.Parameter):
+        return None
+    g = p.grad
+    if g is None or g.dtype != torch.float32 or g.shape != p.shape or not g.is_contiguous() or not g.is_cuda:
+        return None
+    if getattr(p, "_post_accumulate_grad_hooks", None) or getattr(p, "_backward_hooks", None):
+        return None
+    return g
+
+
+DIRECT_GRAD = True
+
+
+def colsum(x: torch.Tensor, out: "torch.Tensor | None" = None) -> "torch.Tensor | None":
+    """Column sums of a contiguous [M, C] fp32 CUDA matrix (C % 4 == 0): the bias gradient of a convolution.
+    With ``out`` the sums are ADDED into it and None is returned."""
     M, C = x.shape
     if not (x.is_cuda and x.is_contiguous() and x.dtype == torch.float32 and C % 4 == 0 and C <= 1024):
-        return x.sum(0)
-    out = torch.empty(C, dtype=torch.float32, device=x.device)
+        if out is None:
+            return x.sum(0)
+        out.add_(x.sum(0))
+        return None
+    acc = out is not None
+    if out is None:
+        out = torch.empty(C, dtype=torch.float32, device=x.device)
     work = torch.empty(int(_lib.cuda().dl_bn_work_bytes(C)) // 8 + 1, dtype=torch.float64, device=x.device)
     with torch.cuda.device(x.device):
-        _lib.check(_lib.cuda().dl_colsum(x.data_ptr(), out.data_ptr(), M, C, work.data_ptr(), _stream(x)))
-    return out
+        _lib.check(_lib.cuda().dl_colsum(x.data_ptr(), out.data_ptr(), M, C, int(acc), work.data_ptr(), _stream(x)))
+    return None if acc else out
 
 
 class _BNReLUPool(torch.autograd.Function):
@@ -41,6 +68,7 @@ class _BNReLUPool(torch.autograd.Function):
                 running_var.data_ptr() if running_var is not None else None, B, H, W, C, float(eps), float(momentum),
                 work.data_ptr(), _stream(y)))
         ctx.save_for_backward(y, gamma, beta, mean, invstd)
+        ctx.params = (gamma, beta)
         return p
 
     @staticmethod
@@ -49,13 +77,17 @@ class _BNReLUPool(torch.autograd.Function):
         B, H, W, C = y.shape
         dp = dp.contiguous()
         dy = torch.empty_like(y)
-        dgamma = torch.empty(C, dtype=torch.float32, device=y.device)
-        dbeta = torch.empty(C, dtype=torch.float32, device=y.device)
+        sink_g, sink_b = grad_sink(ctx.params[0]), grad_sink(ctx.params[1])
+        direct = sink_g is not None and sink_b is not None
+        dgamma = sink_g if direct else torch.empty(C, dtype=torch.float32, device=y.device)
+        dbeta = sink_b if direct else torch.empty(C, dtype=torch.float32, device=y.device)
         work = torch.empty(int(_lib.cuda().dl_bn_work_bytes(C)) // 8 + 1, dtype=torch.float64, device=y.device)
         with torch.cuda.device(y.device):
             _lib.check(_lib.cuda().dl_bn_relu_pool_bwd(
                 y.data_ptr(), dp.data_ptr(), dy.data_ptr(), gamma.data_ptr(), beta.data_ptr(), mean.data_ptr(), invstd.data_ptr(),
-                dgamma.data_ptr(), dbeta.data_ptr(), B, H, W, C, work.data_ptr(), _stream(y)))
+                dgamma.data_ptr(), dbeta.data_ptr(), B, H, W, C, int(direct), work.data_ptr(), _stream(y)))
+        if direct:
+            return dy, None, None, None, None, None, None
         return dy, dgamma, dbeta, None, None, None, None
 
 

@@ -82,11 +82,12 @@ def _implicit_ok(B: int, H: int, W: int, cin: int, cout: int) -> bool:
     return (B * H * W) % 32 == 0
 
 
-def _tc_conv(mode: int, act: torch.Tensor, w: torch.Tensor, out: torch.Tensor, bias, B, H, W, cin, cout, split_k, terms) -> torch.Tensor:
+def _tc_conv(mode: int, act: torch.Tensor, w: torch.Tensor, out: torch.Tensor, bias, B, H, W, cin, cout, split_k, terms,
+             accumulate: bool = False) -> torch.Tensor:
     with torch.cuda.device(act.device):
         _lib.check(_lib.cuda().dl_tc_conv5x5(mode, act.data_ptr(), w.data_ptr(), out.data_ptr(),
-                                             bias.data_ptr() if bias is not None else None, B, H, W, cin, cout, int(split_k), 0,
-                                             int(terms), _stream(act)))
+                                             bias.data_ptr() if bias is not None else None, B, H, W, cin, cout, int(split_k),
+                                             int(accumulate), int(terms), _stream(act)))
     return out
 
 
@@ -104,6 +105,7 @@ class _Conv5x5Implicit(torch.autograd.Function):
         _tc_conv(1, x, weight, y, bias, B, H, W, C, cout, _splits((M + 127) // 128, (cout + bn - 1) // bn, TAPS * C), terms)
         ctx.save_for_backward(x, weight)
         ctx.meta = (terms, bias is not None)
+        ctx.params = (weight, bias)
         return y.view(B, H, W, cout)
 
     @staticmethod
@@ -115,12 +117,17 @@ class _Conv5x5Implicit(torch.autograd.Function):
         M = B * H * W
         dy = dy.contiguous()
         dx = dw = db = None
+        from .bn import colsum, grad_sink
         if ctx.needs_input_grad[1]:
-            dw = torch.empty(cout, kc, dtype=torch.float32, device=x.device)
-            _tc_conv(3, x, dy, dw, None, B, H, W, C, cout, _splits((cout + 127) // 128, (kc + 127) // 128, M), terms)
+            sink = grad_sink(ctx.params[0])
+            if sink is not None:       # the wgrad GEMM's epilogue adds straight into weight.grad (red.add): no extra pass
+                _tc_conv(3, x, dy, sink, None, B, H, W, C, cout, _splits((cout + 127) // 128, (kc + 127) // 128, M), terms,
+                         accumulate=True)
+            else:
+                dw = torch.empty(cout, kc, dtype=torch.float32, device=x.device)
+                _tc_conv(3, x, dy, dw, None, B, H, W, C, cout, _splits((cout + 127) // 128, (kc + 127) // 128, M), terms)
         if has_bias and ctx.needs_input_grad[2]:
-            from .bn import colsum
-            db = colsum(dy.view(M, cout))
+            db = colsum(dy.view(M, cout), out=grad_sink(ctx.params[1]))
         if ctx.needs_input_grad[0]:
             bn = 64 if C <= 64 else 128
             dx = torch.empty(B, H, W, C, dtype=torch.float32, device=x.device)
@@ -146,6 +153,7 @@ class _Conv5x5(torch.autograd.Function):
         y = tc_gemm(col, w, bias=bias, split_k=_splits((M + 127) // 128, (cout + bn - 1) // bn, ld), terms=terms)
         ctx.save_for_backward(col, w)
         ctx.meta = (B, H, W, C, cout, kc, terms, bias is not None)
+        ctx.params = (weight, bias)
         return y.view(B, H, W, cout)
 
     @staticmethod
@@ -161,8 +169,8 @@ class _Conv5x5(torch.autograd.Function):
                               split_k=_splits((cout + 127) // 128, (ld + bn - 1) // bn, M))
             dw = dw_full[:, :kc] if ld != kc else dw_full
         if has_bias and ctx.needs_input_grad[2]:
-            from .bn import colsum
-            db = colsum(dy2)
+            from .bn import colsum, grad_sink
+            db = colsum(dy2, out=grad_sink(ctx.params[1]))
         if ctx.needs_input_grad[0]:
             dcol = tc_gemm(dy2, w, b_mn=True, terms=terms)          # [M, ld]; K = Cout is short, no split
             dx = col2im5x5(dcol, (B, H, W, C))
