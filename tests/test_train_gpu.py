@@ -125,6 +125,34 @@ def test_bucketed_overlap_equals_single_launch(use_graph):
     assert abs(l_a - l_b) < 1e-2
 
 
+def test_prefetch_pipeline_equals_plain_step():
+    """TrainStep.prefetch (H2D of the next batch on a copy stream) + run() trains on exactly the same data as step(x, y)."""
+    from torch_distlearn_b200.models import mnist_convnet
+    from torch_distlearn_b200.parallel.trainer import TrainStep
+    g = torch.Generator().manual_seed(11)
+    xs = [torch.randn(32, 1024, generator=g).pin_memory() for _ in range(5)]
+    ys = [torch.randint(0, 10, (32,), generator=g).pin_memory() for _ in range(5)]
+    losses = []
+    for mode in ("plain", "prefetch"):
+        dl, comm, model, ref, flat = _setup(mnist_convnet)
+        sgd = dl.AllReduceSGD(comm, flat)
+        step = TrainStep(model, flat, sgd, (32, 1024), lr=0.05, use_graph=True, warmup=1)
+        step.capture()
+        out = []
+        if mode == "prefetch":
+            step.prefetch(xs[0], ys[0])
+        for i in range(5):
+            if mode == "plain":
+                step.step(xs[i], ys[i])
+            else:
+                step.run()
+                if i + 1 < 5:
+                    step.prefetch(xs[i + 1], ys[i + 1])
+            out.append(step.loss_value())
+        losses.append(out)
+    torch.testing.assert_close(torch.tensor(losses[1]), torch.tensor(losses[0]), rtol=1e-5, atol=1e-6)
+
+
 def test_allreduce_ea_single_node_and_checkpoint(tmp_path):
     from torch_distlearn_b200.models import mnist_convnet
     dl, comm, model, ref, flat = _setup(mnist_convnet)

@@ -46,6 +46,8 @@ class TrainStep:
         self.use_graph = bool(use_graph and dev.type == "cuda")
         self._warmup = warmup
         self._captured = False
+        self._copy_stream = None
+        self._staged = False
         # bucket_mb > 0: launch the fused kernel per gradient bucket from autograd hooks, overlapped
         # with the rest of backward on a side stream (parallel/bucketed.py)
         self.buckets = None
@@ -117,10 +119,36 @@ class TrainStep:
         self.x.copy_(x, non_blocking=True)
         self.y.copy_(y, non_blocking=True)
 
+    def prefetch(self, x: torch.Tensor, y: torch.Tensor) -> None:
+        """Start copying the NEXT batch (pinned host memory) to the device on a copy stream while the current step
+        is still running; the following ``run()`` picks it up.  The input pipeline of a real trainer: the H2D copy
+        disappears behind the step instead of sitting in front of it."""
+        if self.device.type != "cuda":
+            self.load(x, y)
+            return
+        if self._copy_stream is None:
+            self._copy_stream = torch.cuda.Stream(self.device)
+            self._x_next, self._y_next = torch.empty_like(self.x), torch.empty_like(self.y)
+            self._staged_ev, self._consumed_ev = torch.cuda.Event(), torch.cuda.Event()
+            self._consumed_ev.record(torch.cuda.current_stream(self.device))
+        self._copy_stream.wait_event(self._consumed_ev)          # the previous staged batch has been moved out
+        with torch.cuda.stream(self._copy_stream):
+            self._x_next.copy_(x, non_blocking=True)
+            self._y_next.copy_(y, non_blocking=True)
+            self._staged_ev.record(self._copy_stream)
+        self._staged = True
+
     def run(self) -> torch.Tensor:
-        """One training step on whatever is in the static buffers; returns the (device) loss."""
+        """One training step on whatever is in the static buffers (or on the prefetched batch); returns the (device) loss."""
         if not self._captured:
             self.capture()
+        if self._staged:
+            cur = torch.cuda.current_stream(self.device)
+            cur.wait_event(self._staged_ev)
+            self.x.copy_(self._x_next, non_blocking=True)        # device-to-device, a few microseconds
+            self.y.copy_(self._y_next, non_blocking=True)
+            self._consumed_ev.record(cur)
+            self._staged = False
         if self.graph is not None:
             self.graph.replay()
             self.sgd.steps += 1
