@@ -57,8 +57,9 @@ def reference_arm(args) -> None:
     # The reference is pure Lua/Torch7 (0 Python files, rockspec build type "builtin"); the offline pip
     # install of /root/reference fails for lack of a Python project, and the image has no lua/luajit/th
     # (DESIGN.md "Reference arm").
-    print(json.dumps({"impl": "reference",
-                      "unavailable": "reference is Lua/Torch7 + luarocks ipc: not pip-installable, no lua/th runtime in the image"}))
+    if int(os.environ.get("RANK", "0")) == 0:       # one line per job, also under torchrun
+        print(json.dumps({"impl": "reference",
+                          "unavailable": "reference is Lua/Torch7 + luarocks ipc: not pip-installable, no lua/th runtime in the image"}))
 
 
 def main() -> None:
