@@ -208,6 +208,15 @@ int dl_bn_relu_pool_bwd(const float* y, const float* dp, float* dy, const float*
  * pass the parameters' .grad views so that no separate gradient-accumulation kernel runs. */
 int dl_colsum(const float* x, float* out, long long M, int C, int accumulate, void* work, void* stream);
 
+/* Classifier head: Reshape -> Linear(HW*C, J) -> LogSoftMax -> ClassNLLCriterion (examples/Model.lua:44-52) on an NHWC
+ * feature map feat[B, HW, C]; w[J, HW*C] keeps the reference's (c, h, w) column order.  J = 10 or 16.
+ * forward: logp[B, J], loss[1] = mean NLL (rowloss: B floats of scratch).  backward: gloss = device pointer to the
+ * upstream gradient of the loss; dfeat[B, HW, C], dw[J, HW*C], db[J] (accumulate != 0: added into dw / db). */
+int dl_head_fwd(const float* feat, const float* w, const float* bias, const int64_t* target, float* logp, float* loss,
+                float* rowloss, int B, int HW, int C, int J, void* stream);
+int dl_head_bwd(const float* feat, const float* w, const float* logp, const int64_t* target, const float* gloss, float* dfeat,
+                float* dw, float* db, int B, int HW, int C, int J, int accumulate, void* stream);
+
 /* ---- local flat-vector ops (single GPU, no communication) ---- */
 /* p -= lr * (g*scale [+ wd*p] [momentum]); optionally zero g. world==1 fast path. */
 int dl_local_sgd(float* p, float* g, float* m, uint64_t n, float lr, float momentum,

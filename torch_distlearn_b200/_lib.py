@@ -113,6 +113,8 @@ def cuda():
     _sig(lib, "dl_bn_relu_pool_fwd", i32, [vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, f32, f32, vp, vp])
     _sig(lib, "dl_bn_relu_pool_bwd", i32, [vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp, vp])
     _sig(lib, "dl_colsum", i32, [vp, vp, C.c_longlong, i32, i32, vp, vp])
+    _sig(lib, "dl_head_fwd", i32, [vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, vp])
+    _sig(lib, "dl_head_bwd", i32, [vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp])
     _sig(lib, "dl_im2col5x5", i32, [vp, vp, i32, i32, i32, i32, C.c_longlong, vp])
     _sig(lib, "dl_col2im5x5", i32, [vp, vp, i32, i32, i32, i32, C.c_longlong, vp])
     _sig(lib, "dl_local_sgd", i32, [vp, vp, vp, u64, f32, f32, f32, i32, f32, i32, vp])

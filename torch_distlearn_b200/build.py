@@ -36,6 +36,7 @@ CUDA_SOURCES = [
     "tc_gemm.cu",
     "conv_ops.cu",
     "bn_ops.cu",
+    "head_ops.cu",
 ]
 HOST_SOURCES = ["host_transport.cpp"]
 

@@ -60,6 +60,27 @@ class CifarConvNetTC(nn.Module):
         x = self.linear(x.permute(0, 3, 1, 2).reshape(x.shape[0], 2048))   # (c, h, w) feature order, examples/Model.lua:44
         return F.log_softmax(x, dim=1)
 
+    def features(self, x: torch.Tensor) -> torch.Tensor:
+        """NCHW input batch -> NHWC feature map [B, 2, 2, 512] of the last block (fused tail only)."""
+        x = x.permute(0, 2, 3, 1).contiguous()
+        for conv, bn in zip(self.convs, self.bns):
+            x = bn(conv(x))
+        return x
+
+    def forward_with_loss(self, x: torch.Tensor, target: torch.Tensor):
+        """(log-probabilities, mean NLL loss) with the classifier head fused into two launches (csrc/head_ops.cu);
+        falls back to ``nll_loss(self(x), target)`` where the fused head does not apply (CPU, eval, unfused tail)."""
+        from ..ops.head import head_nll, head_supported
+        if self.fused_tail and self.training and x.is_cuda:
+            feat = self.features(x)
+            if head_supported(feat, self.linear.weight):
+                loss, logp = head_nll(feat, self.linear.weight, self.linear.bias, target)
+                return logp, loss
+            out = F.log_softmax(self.linear(feat.permute(0, 3, 1, 2).reshape(feat.shape[0], 2048)), dim=1)
+            return out, F.nll_loss(out, target)
+        out = self(x)
+        return out, F.nll_loss(out, target)
+
     @torch.no_grad()
     def load_reference(self, ref: CifarConvNet) -> "CifarConvNetTC":
         for mine, theirs in zip(self.convs, ref.convs):

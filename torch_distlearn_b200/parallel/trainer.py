@@ -30,6 +30,7 @@ class TrainStep:
                  bucket_blocks: int = 32):
         self.model, self.flat, self.sgd = model, flat, sgd
         self.lr, self.momentum, self.weight_decay, self.nesterov = lr, momentum, weight_decay, nesterov
+        self._fused_loss = loss_fn is None and hasattr(model, "forward_with_loss")
         self.loss_fn = loss_fn or F.nll_loss          # the models end in log_softmax (ClassNLLCriterion)
         self.variant, self.nblocks = variant, nblocks
         dev = flat.device
@@ -58,8 +59,11 @@ class TrainStep:
 
     # ------------------------------------------------------------------------------------------------
     def _body(self) -> None:
-        out = self.model(self.x)
-        loss = self.loss_fn(out, self.y)
+        if self._fused_loss:
+            out, loss = self.model.forward_with_loss(self.x, self.y)     # classifier head + loss in the model's own kernels
+        else:
+            out = self.model(self.x)
+            loss = self.loss_fn(out, self.y)
         loss.backward()
         self.logits = out.detach()
         self.loss.copy_(loss.detach())
