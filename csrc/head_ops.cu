@@ -105,44 +105,45 @@ __global__ void __launch_bounds__(HEAD_THREADS) head_bwd_feat_kernel(const float
   }
 }
 
-// ---- backward B: weight and bias gradients; each thread owns one feature and walks the batch -------------------
+// ---- backward B: weight and bias gradients; thread = one feature, blockIdx.y = one slice of the batch -----------
+// The batch is cut into gridDim.y slices so that 128 blocks (not 16) share the work; slices meet in dw / db through
+// float atomics (dw / db are the parameters' zeroed-or-accumulating .grad, or were cleared by the host wrapper).
+#define HEAD_SLICES 8
 template <int J>
 __global__ void __launch_bounds__(HEAD_THREADS) head_bwd_w_kernel(const float* __restrict__ feat, const float* __restrict__ logp,
                                                                   const long long* __restrict__ target, const float* __restrict__ gloss,
-                                                                  float* __restrict__ dw, float* __restrict__ db, int B, int HW, int C,
-                                                                  int accumulate) {
-  extern __shared__ float sdl[];  // [B][J]
+                                                                  float* __restrict__ dw, float* __restrict__ db, int B, int HW, int C) {
+  extern __shared__ float sdl[];  // [slice of B][J]
   const int F = HW * C;
+  const int per = (B + gridDim.y - 1) / gridDim.y;
+  const int b0 = blockIdx.y * per, b1 = min(B, b0 + per);
   const float scale = gloss[0] / static_cast<float>(B);
-  for (int i = threadIdx.x; i < B; i += HEAD_THREADS) {
+  for (int i = b0 + threadIdx.x; i < b1; i += HEAD_THREADS) {
     float dl[J];
     head_dlogits<J>(logp, target, i, scale, dl);
 #pragma unroll
-    for (int j = 0; j < J; ++j) sdl[i * J + j] = dl[j];
+    for (int j = 0; j < J; ++j) sdl[(i - b0) * J + j] = dl[j];
   }
   __syncthreads();
   const int idx = blockIdx.x * HEAD_THREADS + threadIdx.x;
-  if (idx < F) {
+  if (idx < F && b1 > b0) {
     float acc[J];
 #pragma unroll
     for (int j = 0; j < J; ++j) acc[j] = 0.f;
-    for (int b = 0; b < B; ++b) {
+    for (int b = b0; b < b1; ++b) {
       const float v = feat[static_cast<long long>(b) * F + idx];
 #pragma unroll
-      for (int j = 0; j < J; ++j) acc[j] = fmaf(sdl[b * J + j], v, acc[j]);
+      for (int j = 0; j < J; ++j) acc[j] = fmaf(sdl[(b - b0) * J + j], v, acc[j]);
     }
     const int hw = idx / C, c = idx - hw * C;
     float* out = dw + c * HW + hw;
 #pragma unroll
-    for (int j = 0; j < J; ++j) {
-      float* o = out + static_cast<long long>(j) * F;
-      *o = (accumulate ? *o : 0.f) + acc[j];
-    }
+    for (int j = 0; j < J; ++j) atomicAdd(out + static_cast<long long>(j) * F, acc[j]);
   }
-  if (blockIdx.x == 0 && threadIdx.x < J) {
+  if (blockIdx.x == 0 && threadIdx.x < J && b1 > b0) {
     float a = 0.f;
-    for (int b = 0; b < B; ++b) a += sdl[b * J + threadIdx.x];
-    db[threadIdx.x] = (accumulate ? db[threadIdx.x] : 0.f) + a;
+    for (int b = b0; b < b1; ++b) a += sdl[(b - b0) * J + threadIdx.x];
+    atomicAdd(db + threadIdx.x, a);
   }
 }
 
@@ -181,8 +182,14 @@ extern "C" int dl_head_bwd(const float* feat, const float* w, const float* logp,
   HEAD_DISPATCH(J, (head_bwd_feat_kernel<J><<<B, HEAD_THREADS, 0, st>>>(w, logp, tg, gloss, dfeat, B, HW, C)));
   dl_note_launch();
   DL_CUDA(cudaGetLastError());
-  HEAD_DISPATCH(J, (head_bwd_w_kernel<J><<<(F + HEAD_THREADS - 1) / HEAD_THREADS, HEAD_THREADS, static_cast<size_t>(B) * J * sizeof(float), st>>>(
-                       feat, logp, tg, gloss, dw, db, B, HW, C, accumulate)));
+  if (!accumulate) {   // the slices add with atomics: start from zero unless the caller's buffers already accumulate
+    DL_CUDA(cudaMemsetAsync(dw, 0, static_cast<size_t>(J) * F * sizeof(float), st));
+    DL_CUDA(cudaMemsetAsync(db, 0, static_cast<size_t>(J) * sizeof(float), st));
+  }
+  const int slices = B >= HEAD_SLICES * 4 ? HEAD_SLICES : 1;
+  const int per = (B + slices - 1) / slices;
+  HEAD_DISPATCH(J, (head_bwd_w_kernel<J><<<dim3((F + HEAD_THREADS - 1) / HEAD_THREADS, slices), HEAD_THREADS,
+                                            static_cast<size_t>(per) * J * sizeof(float), st>>>(feat, logp, tg, gloss, dw, db, B, HW, C)));
   dl_note_launch();
   DL_CUDA(cudaGetLastError());
   return DL_OK;

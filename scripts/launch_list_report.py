@@ -12,7 +12,7 @@ names = [(r[ki], float(r[vi].replace(",", "")) / 1000.0) for r in data if len(r)
 idx = [i for i, (n, _) in enumerate(names) if "sgd_twoshot" in n]
 step = names[idx[-2] + 1: idx[-1] + 1]
 tot = sum(v for _, v in step)
-ours = ("tc_gemm", "bn_", "im2col", "col2im", "colsum", "sgd_", "fused_ea", "allreduce")
+ours = ("tc_gemm", "bn_", "im2col", "col2im", "colsum", "sgd_", "fused_ea", "allreduce", "head_")
 agg = collections.OrderedDict()
 for n, v in step:
     short = n.split("(")[0].replace("void ", "").replace("<unnamed>::", "")[:60]
@@ -22,7 +22,7 @@ for n, v in step:
 mine = sum(v for n, v in step if any(k in n for k in ours))
 print(f"# Kernels of one training step (flagship: CIFAR convnet, batch 128, 1 x B200)\n")
 print("`ncu --metrics gpu__time_duration.sum --clock-control none` over `python scripts/step_once.py 4` (eager launches,")
-print("cold caches, serialised: read the SHARES, not the absolute times; the step runs in 1.45 ms as a CUDA graph).\n")
+print("cold caches, serialised: read the SHARES, not the absolute times; the step runs in 1.17 ms as a CUDA graph).\n")
 print(f"{len(step)} kernels, {tot:.0f} us in total; {100 * mine / tot:.0f} % of the time is in this library's own kernels.\n")
 print("| kernel | launches | us | share |")
 print("|---|---|---|---|")
