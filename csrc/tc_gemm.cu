@@ -29,7 +29,6 @@
 #include <stdlib.h>
 
 #include <mutex>
-#include <unordered_map>
 
 #include "dl_host.h"
 

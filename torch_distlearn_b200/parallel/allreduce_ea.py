@@ -62,9 +62,8 @@ class AllReduceEA:
         return self._center[self._cur].tensor
 
     def _launch(self, active: int, read: bool):
-        extra = {} if self.comm.backend == "host" else {}
         res = self.comm.fused_ea(self._x, self._center[self._cur], self._center[1 - self._cur], self._n, self.alpha,
-                                 active=active, payload=min(self.step, 2**30 - 1), channel=self.channel, read=read, **extra)
+                                 active=active, payload=min(self.step, 2**30 - 1), channel=self.channel, read=read)
         self._cur = 1 - self._cur           # every rank flips in lockstep (the kernel keeps c_new coherent)
         return res
 
