@@ -25,6 +25,7 @@ def _worker(rank, world, job, port, scenario, kwargs):
     try:
         return dist_checks.SCENARIOS[scenario][0](comm, rank, world, **kwargs)
     finally:
+        comm.close()
         dist.barrier()
         dist.destroy_process_group()
 
@@ -34,6 +35,8 @@ def _worker(rank, world, job, port, scenario, kwargs):
     ("sgd_fused_uneven", 2, {}),
     ("ea_reference_test", 2, {"seed": 22, "use_flat": True}),
     ("tree_and_metrics", 2, {}),
+    ("async_ea", 3, {"exclusive": True, "with_tester": False}),
+    ("async_ea", 4, {"exclusive": False, "with_tester": True}),
 ])
 def test_scenarios_over_torch_distributed(scenario, world, kwargs):
     results = run_ranks(_worker, world, _free_port(), scenario, kwargs, timeout=240.0)

@@ -694,8 +694,8 @@ class DistCommunicator(Communicator):
     a mix of CPU and GPU nodes (examples/client_remote.sh:5-6).  The heap is a private tensor (offsets
     still match across ranks, nothing is mapped remotely) and every operation is a library collective
     (NCCL when every node is a GPU, gloo with host staging otherwise) followed by the local math — the
-    reference's dataflow, kept as the portability path.  One-sided AsyncEA needs peer-mapped memory and
-    is not available here."""
+    reference's dataflow, kept as the portability path.  AsyncEA works here the reference's way: the rank
+    that owns the center serves pull / push requests from a service thread, one client at a time."""
 
     backend = "dist"
 
@@ -713,6 +713,7 @@ class DistCommunicator(Communicator):
         self._bytes = torch.zeros(heap_bytes, dtype=torch.uint8, device=device)
         self._wire_cpu = dist.get_backend(group) != "nccl"       # gloo: CUDA tensors are staged through the host
         self._last: Optional[CommResult] = None
+        self._start_service()
 
     def _local_bytes(self) -> torch.Tensor:
         return self._bytes
@@ -815,11 +816,127 @@ class DistCommunicator(Communicator):
     def read_result(self, channel: int = 0, stream=None) -> CommResult:
         return self._last if self._last is not None else CommResult(0, [0] * self.world)
 
-    def _no_async(self, *_a, **_k):
-        raise NotImplementedError("AsyncEA needs peer-mapped memory (P2PCommunicator / HostCommunicator); "
-                                  "the torch.distributed backend has no one-sided operations")
+    # -- asynchronous EASGD over messages ----------------------------------------------------------------
+    # Without peer-mapped memory the center has to be served by its owner, which is the reference's own design
+    # (lua/AsyncEA.lua:163-228): a service thread on every rank answers requests against the local heap and
+    # mailbox, one at a time — so syncs are always exclusive here.  Requests travel on a private gloo group:
+    # tag 0 = request header, tag 1 = server -> client payload, tag 2 = client -> server payload.
+    _OP_STOP, _OP_MB_WRITE, _OP_MB_READ, _OP_SYNC_COUNT, _OP_PULL, _OP_SYNC = 0, 1, 2, 3, 4, 5
 
-    async_client_sync = peer_pull = sync_count = mailbox_write = mailbox_read = _no_async
+    def _start_service(self) -> None:
+        import threading
+        self._mailbox = [0] * 32
+        self._sync_count = 0
+        self._svc_lock = threading.Lock()
+        self._agroup = self._dist.new_group(backend="gloo") if self.world > 1 else None
+        self._svc = None
+        if self.world > 1:
+            self._svc = threading.Thread(target=self._serve, name="distlearn-async-service", daemon=True)
+            self._svc.start()
+
+    def _heap_f32(self, off: int, n: int) -> torch.Tensor:
+        return self._bytes[off:off + 4 * n].view(torch.float32)
+
+    def _serve(self) -> None:
+        dist, g = self._dist, self._agroup
+        hdr = torch.zeros(4, dtype=torch.int64)
+        while True:
+            try:
+                src = dist.recv(hdr, group=g, tag=0)
+            except Exception:  # noqa: BLE001 - the process group went away
+                return
+            op, a, b, c = (int(v) for v in hdr.tolist())
+            if op == self._OP_STOP:
+                return
+            with self._svc_lock:
+                if op == self._OP_MB_WRITE:
+                    self._mailbox[a] = b
+                    dist.send(torch.zeros(1, dtype=torch.int64), dst=src, group=g, tag=1)     # ack: the write is visible
+                elif op == self._OP_MB_READ:
+                    dist.send(torch.tensor([self._mailbox[a]], dtype=torch.int64), dst=src, group=g, tag=1)
+                elif op == self._OP_SYNC_COUNT:
+                    dist.send(torch.tensor([self._sync_count], dtype=torch.int64), dst=src, group=g, tag=1)
+                elif op in (self._OP_PULL, self._OP_SYNC):
+                    center = self._heap_f32(a, b)
+                    dist.send(center.detach().cpu().contiguous(), dst=src, group=g, tag=1)
+                    if op == self._OP_SYNC:
+                        delta = torch.empty(b, dtype=torch.float32)
+                        dist.recv(delta, src=src, group=g, tag=2)
+                        center.add_(delta.to(center.device))                                  # lua/AsyncEA.lua:212-216
+                        self._sync_count += 1
+
+    def _request(self, server: int, op: int, a: int = 0, b: int = 0, c: int = 0) -> None:
+        self._dist.send(torch.tensor([op, a, b, c], dtype=torch.int64), dst=server, group=self._agroup, tag=0)
+
+    def _reply_i64(self, server: int) -> int:
+        t = torch.zeros(1, dtype=torch.int64)
+        self._dist.recv(t, src=server, group=self._agroup, tag=1)
+        return int(t[0])
+
+    def mailbox_write(self, rank: int, index: int, value: int) -> None:
+        if rank == self.rank:
+            with self._svc_lock:
+                self._mailbox[index] = int(value)
+            return
+        self._request(rank, self._OP_MB_WRITE, index, int(value))
+        self._reply_i64(rank)
+
+    def mailbox_read(self, rank: int, index: int) -> int:
+        if rank == self.rank:
+            with self._svc_lock:
+                return self._mailbox[index]
+        self._request(rank, self._OP_MB_READ, index)
+        return self._reply_i64(rank)
+
+    def sync_count(self, server: int) -> int:
+        if server == self.rank:
+            with self._svc_lock:
+                return self._sync_count
+        self._request(server, self._OP_SYNC_COUNT)
+        return self._reply_i64(server)
+
+    def peer_pull(self, src_rank: int, buf: SymBuffer, dst: torch.Tensor, n: Optional[int] = None, stream=None) -> None:
+        n = buf.numel if n is None else n
+        if src_rank == self.rank:
+            dst.view(-1)[:n].copy_(buf.tensor[:n])
+            return
+        self._request(src_rank, self._OP_PULL, buf.offset, n)
+        t = torch.empty(n, dtype=torch.float32)
+        self._dist.recv(t, src=src_rank, group=self._agroup, tag=1)
+        dst.view(-1)[:n].copy_(t)
+
+    def async_client_sync(self, server: int, x: torch.Tensor, center: SymBuffer, n: int, alpha: float, exclusive: bool = False,
+                          nblocks: int = 0, stream=None) -> None:
+        """d = alpha (x - c); x -= d; c += d with c on ``server`` (lua/AsyncEA.lua:95-132): pull, local move, push."""
+        xv = x.view(-1)[:n]
+        if server == self.rank:
+            with self._svc_lock:
+                c = center.tensor[:n]
+                d = (xv - c) * alpha
+                xv.sub_(d)
+                c.add_(d)
+                self._sync_count += 1
+            self.launches += 1
+            return
+        self._request(server, self._OP_SYNC, center.offset, n)
+        c = torch.empty(n, dtype=torch.float32)
+        self._dist.recv(c, src=server, group=self._agroup, tag=1)
+        xc = xv.detach().cpu() if xv.is_cuda else xv
+        d = (xc - c) * alpha                                                   # lua/AsyncEA.lua:114
+        self._dist.send(d.contiguous(), dst=server, group=self._agroup, tag=2)
+        xv.sub_(d.to(xv.device))                                               # lua/AsyncEA.lua:115
+        self.launches += 1
+
+    def close(self) -> None:
+        """Collective: every rank stops the service thread of its right-hand neighbour, then waits for its own."""
+        if getattr(self, "_svc", None) is not None:
+            try:
+                self._dist.barrier(group=self._group)                         # nobody is mid-request any more
+                self._request((self.rank + 1) % self.world, self._OP_STOP)
+                self._svc.join(timeout=10)
+            except Exception:  # noqa: BLE001
+                pass
+            self._svc = None
 
     def synchronize(self) -> None:
         if self.device.type == "cuda":
