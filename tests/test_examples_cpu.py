@@ -48,3 +48,21 @@ def test_async_easgd_server_clients_tester(tmp_path):
     log = open(tmp_path / "ErrorRate.log").read().strip().splitlines()
     assert log[0].startswith("Training Error") and len(log) >= 2
     assert (tmp_path / "easgd_center.dlb200").exists()
+
+
+def test_cifar10_two_cpu_processes(tmp_path):
+    """examples/cifar10.py (C8): global batch split over the nodes, train + test pass per epoch, confusion matrix all-reduce."""
+    metrics = tmp_path / "c.jsonl"
+    rc = _spawn("cifar10.py", 2, 8205, "--numEpochs", "1", "--trainSamples", "192", "--testSamples", "64", "--batchSize", "16",
+                "--learningRate", "0.01", "--metrics", str(metrics))
+    assert rc == 0
+    import json
+    row = json.loads(open(metrics).read().strip().splitlines()[-1])
+    assert row["epoch"] == 1 and 0.0 <= row["test_accuracy"] <= 1.0 and row["samples_per_s"] > 0
+
+
+def test_client_remote_over_torch_distributed():
+    """examples/client_remote.py (C15): the AllReduceEA flow with rendezvous on --host/--port (torch.distributed backend)."""
+    rc = _spawn("client_remote.py", 2, 8206, "--numEpochs", "1", "--trainSamples", "128", "--testSamples", "64", "--batchSize", "16",
+                "--learningRate", "0.01", "--tau", "2")
+    assert rc == 0
