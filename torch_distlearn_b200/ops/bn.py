@@ -19,16 +19,25 @@ def grad_sink(p) -> "torch.Tensor | None":
     Autograd adds a returned gradient into ``p.grad`` with one extra element-wise kernel per parameter; the
     backward kernels of this package can add into ``p.grad`` themselves (it is a view of the flat gradient vector,
     zeroed by the fused SGD kernel).  That is only done when it is indistinguishable from autograd's accumulation:
-    ``p.grad`` exists, is dense fp32 of the parameter's shape, and nobody listens for the accumulation event
-    (post-accumulate hooks, e.g. GradBuckets, still get the ordinary path)."""
+    ``p.grad`` exists and is dense fp32 of the parameter's shape, and no tensor hook wants to see (or change) the
+    incoming gradient.  Whoever writes into the sink must call :func:`grad_done` afterwards."""
     if not DIRECT_GRAD or not isinstance(p, torch.nn.Parameter):
         return None
     g = p.grad
     if g is None or g.dtype != torch.float32 or g.shape != p.shape or not g.is_contiguous() or not g.is_cuda:
         return None
-    if getattr(p, "_post_accumulate_grad_hooks", None) or getattr(p, "_backward_hooks", None):
+    if getattr(p, "_backward_hooks", None):
         return None
     return g
+
+
+def grad_done(p) -> None:
+    """Run the parameter's post-accumulate-grad hooks (e.g. GradBuckets' "this bucket is ready") after a backward
+    kernel has been enqueued that adds into ``p.grad`` directly — autograd would have run them after its own add."""
+    hooks = getattr(p, "_post_accumulate_grad_hooks", None)
+    if hooks:
+        for h in list(hooks.values()):
+            h(p)
 
 
 DIRECT_GRAD = True
@@ -87,6 +96,8 @@ class _BNReLUPool(torch.autograd.Function):
                 y.data_ptr(), dp.data_ptr(), dy.data_ptr(), gamma.data_ptr(), beta.data_ptr(), mean.data_ptr(), invstd.data_ptr(),
                 dgamma.data_ptr(), dbeta.data_ptr(), B, H, W, C, int(direct), work.data_ptr(), _stream(y)))
         if direct:
+            grad_done(ctx.params[0])
+            grad_done(ctx.params[1])
             return dy, None, None, None, None, None, None
         return dy, dgamma, dbeta, None, None, None, None
 

@@ -117,7 +117,7 @@ class _Conv5x5Implicit(torch.autograd.Function):
         M = B * H * W
         dy = dy.contiguous()
         dx = dw = db = None
-        from .bn import colsum, grad_sink
+        from .bn import colsum, grad_done, grad_sink
         if ctx.needs_input_grad[1]:
             sink = grad_sink(ctx.params[0])
             if sink is not None:       # the wgrad GEMM's epilogue adds straight into weight.grad (red.add): no extra pass
@@ -132,6 +132,10 @@ class _Conv5x5Implicit(torch.autograd.Function):
             bn = 64 if C <= 64 else 128
             dx = torch.empty(B, H, W, C, dtype=torch.float32, device=x.device)
             _tc_conv(2, dy, weight, dx, None, B, H, W, C, cout, _splits((M + 127) // 128, (C + bn - 1) // bn, TAPS * cout), terms)
+        # only now, with the dgrad GEMM (which reads the weights) enqueued, may a listener start updating this layer
+        for p, g in zip(ctx.params, (dw, db)):
+            if p is not None and g is None:
+                grad_done(p)
         return dx, dw, db, None
 
 
@@ -169,11 +173,13 @@ class _Conv5x5(torch.autograd.Function):
                               split_k=_splits((cout + 127) // 128, (ld + bn - 1) // bn, M))
             dw = dw_full[:, :kc] if ld != kc else dw_full
         if has_bias and ctx.needs_input_grad[2]:
-            from .bn import colsum, grad_sink
+            from .bn import colsum, grad_done, grad_sink
             db = colsum(dy2, out=grad_sink(ctx.params[1]))
         if ctx.needs_input_grad[0]:
             dcol = tc_gemm(dy2, w, b_mn=True, terms=terms)          # [M, ld]; K = Cout is short, no split
             dx = col2im5x5(dcol, (B, H, W, C))
+        if has_bias and ctx.needs_input_grad[2] and db is None:
+            grad_done(ctx.params[1])
         return dx, dw, db, None
 
 

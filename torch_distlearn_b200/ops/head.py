@@ -6,7 +6,7 @@ from __future__ import annotations
 import torch
 
 from .. import _lib
-from .bn import grad_sink
+from .bn import grad_done, grad_sink
 
 
 def _stream(t: torch.Tensor) -> int:
@@ -47,6 +47,8 @@ class _HeadNLL(torch.autograd.Function):
                                                dfeat.data_ptr(), dw.data_ptr(), db.data_ptr(), B, H * W, C, J, int(direct),
                                                _stream(feat)))
         if direct:
+            grad_done(ctx.params[0])
+            grad_done(ctx.params[1])
             return dfeat, None, None, None
         return dfeat, dw, db, None
 

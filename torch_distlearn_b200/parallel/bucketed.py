@@ -57,6 +57,8 @@ class GradBuckets:
                 self.buckets.append(b)
                 end, count, members = start, 0, []
         self._next = 0                      # next bucket to launch (fixed order)
+        self._fired = [False] * len(flat.sizes)
+        self.launched_from_hooks = 0        # buckets that went out DURING backward (the overlap), for tests / diagnostics
         self._hyper = dict(lr=0.01, momentum=0.0, weight_decay=0.0, nesterov=False)
         self._handles = []
         for i, p in enumerate(flat._params):
@@ -72,11 +74,16 @@ class GradBuckets:
 
     def _make_hook(self, index: int):
         def hook(_param):
-            if not self.enabled:
+            # once per parameter per step: the hook can be reached both from a backward kernel that wrote .grad itself
+            # (ops.bn.grad_done) and from autograd's own accumulation node
+            if not self.enabled or self._fired[index]:
                 return
+            self._fired[index] = True
             b = self.buckets[self._bucket_of_param[index]]
             b.pending -= 1
+            before = self._next
             self._launch_ready()
+            self.launched_from_hooks += self._next - before
         return hook
 
     def set_hyper(self, lr: float, momentum: float = 0.0, weight_decay: float = 0.0, nesterov: bool = False) -> None:
@@ -112,6 +119,7 @@ class GradBuckets:
         if self.stream is not None:
             torch.cuda.current_stream(self.device).wait_stream(self.stream)
         self._next = 0
+        self._fired = [False] * len(self._fired)
         for b in self.buckets:
             b.pending = b.n_params
         self.sgd.steps += 1

@@ -92,7 +92,10 @@ class TrainStep:
 
     def capture(self) -> None:
         """Warm up eagerly on the current contents of the static buffers (loads modules, lets cuDNN
-        pick algorithms; these ARE real training steps), then capture one step when graphs are on."""
+        pick algorithms; these ARE real training steps), then capture one step when graphs are on.
+        ``step(x, y)`` loads the batch first, so the warm-up runs on real data; call ``load()`` before an explicit
+        ``capture()`` for the same reason — the buffers start as zeros, and training BatchNorm layers on constant
+        activations is a degenerate (variance 0) step."""
         if self._captured:
             return
         self._captured = True
