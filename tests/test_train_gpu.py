@@ -93,6 +93,32 @@ def test_graph_replay_equals_eager():
     assert torch.isfinite(p_g).all()
 
 
+@pytest.mark.parametrize("use_graph", [False, True])
+def test_capture_leaves_the_training_state_untouched(use_graph):
+    """The warm-up steps inside capture() are full steps, but parameters, momentum, BatchNorm statistics and the step
+    counter come back bit for bit."""
+    from torch_distlearn_b200.models import cifar_convnet_tc
+    from torch_distlearn_b200.parallel.trainer import TrainStep
+    dl, comm, model, ref, flat = _setup(cifar_convnet_tc, with_momentum=True)
+    sgd = dl.AllReduceSGD(comm, flat)
+    flat.momentum.tensor.normal_()
+    step = TrainStep(model, flat, sgd, (16, 3, 32, 32), lr=0.05, momentum=0.9, use_graph=use_graph, warmup=2)
+    g = torch.Generator().manual_seed(11)
+    step.load(torch.randn(16, 3, 32, 32, generator=g), torch.randint(0, 10, (16,), generator=g))
+    before = (flat.params.tensor.clone(), flat.momentum.tensor.clone(), [b.clone() for b in model.buffers()], sgd.steps)
+    launches = comm.launches
+    step.capture()
+    torch.cuda.synchronize()
+    assert comm.launches == launches + 2                      # the warm-up really ran
+    assert torch.equal(flat.params.tensor, before[0]) and torch.equal(flat.momentum.tensor, before[1])
+    for b, old in zip(model.buffers(), before[2]):
+        assert torch.equal(b, old)
+    assert sgd.steps == before[3] and float(flat.grads.tensor.abs().max()) == 0.0
+    step.run()
+    torch.cuda.synchronize()
+    assert not torch.equal(flat.params.tensor, before[0]) and sgd.steps == before[3] + 1
+
+
 @pytest.mark.parametrize("model_kind", ["cudnn", "tc"])
 @pytest.mark.parametrize("use_graph", [False, True])
 def test_bucketed_overlap_equals_single_launch(use_graph, model_kind):
@@ -109,9 +135,7 @@ def test_bucketed_overlap_equals_single_launch(use_graph, model_kind):
         step = TrainStep(model, flat, sgd, (16, 3, 32, 32), lr=0.002, momentum=0.9, use_graph=use_graph, warmup=1,
                          bucket_mb=bucket_mb, bucket_blocks=8)
         g = torch.Generator().manual_seed(5)
-        # warm up on a real batch: on the all-zero static buffers every BatchNorm sees constant activations (variance 0),
-        # 1/sqrt(eps) amplifies last-bit noise of the split-K atomics into different ReLU masks, and two runs of the SAME
-        # configuration already disagree by 1e-1 in the BN biases (scripts/bucket_probe.py)
+        # warm up on a real batch rather than on the all-zero static buffers (BatchNorm on constant activations)
         step.load(torch.randn(16, 3, 32, 32, generator=g), torch.randint(0, 10, (16,), generator=g))
         step.capture()
         if bucket_mb:

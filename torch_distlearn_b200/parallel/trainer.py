@@ -27,7 +27,7 @@ class TrainStep:
                  lr: float, momentum: float = 0.0, weight_decay: float = 0.0, nesterov: bool = False,
                  loss_fn: Optional[Callable] = None, use_graph: bool = True, variant: str = "auto",
                  target_dtype: torch.dtype = torch.int64, warmup: int = 3, nblocks: int = 0, bucket_mb: float = 0.0,
-                 bucket_blocks: int = 32):
+                 bucket_blocks: int = 32, restore_warmup: bool = True):
         self.model, self.flat, self.sgd = model, flat, sgd
         self.lr, self.momentum, self.weight_decay, self.nesterov = lr, momentum, weight_decay, nesterov
         self._fused_loss = loss_fn is None and hasattr(model, "forward_with_loss")
@@ -46,6 +46,7 @@ class TrainStep:
         self._replayed_kernels = 0
         self.use_graph = bool(use_graph and dev.type == "cuda")
         self._warmup = warmup
+        self._restore_warmup = restore_warmup
         self._captured = False
         self._copy_stream = None
         self._staged = False
@@ -73,6 +74,21 @@ class TrainStep:
             self.sgd.step(self.flat, lr=self.lr, momentum=self.momentum, weight_decay=self.weight_decay,
                           nesterov=self.nesterov, zero_grads=True, variant=self.variant, nblocks=self.nblocks)
 
+    def _snapshot(self):
+        flat = self.flat
+        return (flat.params.tensor.clone(), flat.momentum.tensor.clone() if flat.momentum is not None else None,
+                [b.clone() for b in self.model.buffers()], self.sgd.steps)
+
+    def _restore(self, saved) -> None:
+        params, momentum, buffers, steps = saved
+        with torch.no_grad():
+            self.flat.params.tensor.copy_(params)       # identical on every rank before and after: nothing to re-sync
+            if momentum is not None:
+                self.flat.momentum.tensor.copy_(momentum)
+            for b, old in zip(self.model.buffers(), buffers):
+                b.copy_(old)
+        self.sgd.steps = steps
+
     def _native_count(self) -> int:
         if self.device.type != "cuda":
             return self.sgd.comm.launches
@@ -92,10 +108,10 @@ class TrainStep:
 
     def capture(self) -> None:
         """Warm up eagerly on the current contents of the static buffers (loads modules, lets cuDNN
-        pick algorithms; these ARE real training steps), then capture one step when graphs are on.
-        ``step(x, y)`` loads the batch first, so the warm-up runs on real data; call ``load()`` before an explicit
-        ``capture()`` for the same reason — the buffers start as zeros, and training BatchNorm layers on constant
-        activations is a degenerate (variance 0) step."""
+        pick algorithms), then capture one step when graphs are on.  The warm-up steps are full steps — every rank
+        launches the collectives — but they leave no trace: parameters, momentum, the module's buffers (BatchNorm
+        running statistics) and the step counter are put back afterwards, so training starts from the state the caller
+        prepared.  ``step(x, y)`` loads the batch first, so the warm-up sees real data; the buffers start as zeros."""
         if self._captured:
             return
         self._captured = True
@@ -105,8 +121,11 @@ class TrainStep:
         side = torch.cuda.Stream(self.device)
         side.wait_stream(torch.cuda.current_stream(self.device))
         with torch.cuda.stream(side):
+            saved = self._snapshot() if self._restore_warmup else None
             for _ in range(max(self._warmup, 1)):
                 self._eager()
+            if saved is not None:
+                self._restore(saved)
         torch.cuda.current_stream(self.device).wait_stream(side)
         torch.cuda.synchronize(self.device)
         if not self.use_graph:
