@@ -3,8 +3,8 @@
 // "zero the losers + all-reduce" winner broadcast (lua/AllReduceSGD.lua:43-47).
 //
 //   one-shot : every rank pulls the whole vector from the root (small messages)
-//   two-shot : rank j pulls slice j from the root and pushes it to every other rank in the same
-//              pass, so the root's NVLink egress is S instead of (N-1) S
+//   two-shot : every non-root rank pulls one of N-1 slices from the root and pushes it to the other
+//              ranks in the same pass, so the root's NVLink egress is S instead of (N-1) S
 //   NVLS     : the root streams its vector through one multimem.st per 16 bytes; the switch
 //              replicates it to all ranks
 // With off2 != 0 every rank also receives the values at off2 (EA: center <- params,
@@ -55,7 +55,13 @@ __global__ void __launch_bounds__(DL_THREADS, 1) broadcast_kernel(dl_comm_t c, B
         }
       }
     } else if (kVariant == DL_VARIANT_TWOSHOT) {
-      const DlSlice s = dl_slice(a.n4, rank, world);
+      // Slices are owned by the NON-root ranks only (world > 1): the root's NVLink egress is then S — every byte leaves
+      // it exactly once — instead of S (pulls) + S (N-1)/N (pushes of a slice of its own), which is what bounded the
+      // large-message broadcast (1 GiB, 8 GPUs: 2.48 ms = 1.75 S at 770 GB/s).  The root only takes part in the barriers.
+      const int owners = world > 1 ? world - 1 : 1;
+      const int me = world > 1 ? (rank < a.root ? rank : rank - 1) : 0;
+      DlSlice s = dl_slice(a.n4, me, owners);
+      if (world > 1 && rank == a.root) s.begin = s.end = 0;
       for (unsigned long long i0 = s.begin + tid0; i0 < s.end; i0 += stride * U) {
         float4 v[U];
 #pragma unroll
@@ -134,7 +140,8 @@ extern "C" int dl_broadcast(const dl_comm_t* c, uint64_t off, uint64_t off2, uin
   DL_REQUIRE(payload < (1u << 30), "dl_broadcast: payload must fit 30 bits");
   BcArgs a;
   a.off = off; a.off2 = off2; a.n4 = n / 4; a.root = root; a.payload = payload; a.channel = channel;
-  const unsigned long long work = variant == DL_VARIANT_TWOSHOT ? (a.n4 + c->world - 1) / (c->world > 0 ? c->world : 1) : a.n4;
+  const int owners = c->world > 1 ? c->world - 1 : 1;
+  const unsigned long long work = variant == DL_VARIANT_TWOSHOT ? (a.n4 + owners - 1) / owners : a.n4;
   int nb = dl_check_comm(c, channel, dl_pick_blocks(work, 4, nblocks));
   if (nb < 0) return nb;
   cudaStream_t st = static_cast<cudaStream_t>(stream);

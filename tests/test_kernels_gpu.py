@@ -165,7 +165,7 @@ def test_fused_ea(world):
         assert torch.equal(nxt_views[r], cur_views[r])
 
 
-@pytest.mark.parametrize("world,root", [(2, 1), (4, 2), (8, 7), (3, 0)])
+@pytest.mark.parametrize("world,root", [(1, 0), (2, 1), (4, 2), (8, 7), (8, 0), (5, 3), (3, 0)])
 @pytest.mark.parametrize("variant", ["oneshot", "twoshot"])
 def test_broadcast(world, root, variant):
     n = 30016
