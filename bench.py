@@ -44,6 +44,8 @@ def parse():
                    help="ours: tc = convolutions as implicit GEMMs on tcgen05 (3xTF32, fp32-level accuracy, csrc/tc_gemm.cu); "
                         "cudnn = stock torch modules (what the nccl baseline always uses)")
     p.add_argument("--conv-terms", type=int, default=3, choices=[1, 3], help="3 = 3xTF32 (fp32-accurate), 1 = plain TF32")
+    p.add_argument("--flat-order", choices=["module", "execution"], default="module",
+                   help="layout of the flat parameter vector; 'execution' lets --bucket-mb buckets leave layer by layer")
     p.add_argument("--bucket-mb", type=float, default=0.0,
                    help="ours: launch the fused kernel per gradient bucket of this size, overlapped with backward (0 = one launch)")
     p.add_argument("--bucket-blocks", type=int, default=32, help="CTAs per bucket launch (leaves the other SMs to cuDNN)")
@@ -119,7 +121,7 @@ def main() -> None:
         import torch_distlearn_b200 as dl
         from torch_distlearn_b200.parallel.trainer import TrainStep
         comm = dl.P2PCommunicator(rank=rank, world=world, device=dev, heap_mb=args.heap_mb)
-        flat = dl.FlatParams(comm, model)
+        flat = dl.FlatParams(comm, model, order=args.flat_order)
         sgd = dl.AllReduceSGD(comm, flat)
         sgd.synchronizeParameters()
         step = TrainStep(model, flat, sgd, (B, 3, 32, 32), lr=args.lr, use_graph=bool(args.graph), variant=args.variant,
@@ -251,7 +253,7 @@ def main() -> None:
             "data": "synthetic CIFAR-shaped 3x32x32, random-init weights", "impl": args.impl,
             "config": {"model": "cifar10_convnet (examples/Model.lua, 4,328,970 params)", "global_batch": total,
                        "per_gpu_batch": B, "seq_len": None, "parallelism": f"dp{world}", "lr": args.lr,
-                       "tf32": bool(args.tf32), "conv": conv_desc, "cuda_graph": bool(args.graph), "bucket_mb": args.bucket_mb,
+                       "tf32": bool(args.tf32), "conv": conv_desc, "cuda_graph": bool(args.graph), "bucket_mb": args.bucket_mb, "flat_order": args.flat_order,
                        "l2": "no explicit flush: each step streams >126 MB of activations/gradients (working set > L2)",
                        "transport": describe},
             "e2e": {"value": round(e2e_value, 1), "unit": "samples/s", "h2d_bytes_per_step": h2d_bytes,

@@ -28,6 +28,8 @@ def main(argv=None):
     p = base_parser("CIFAR-10 AllReduceSGD (examples/cifar10.lua)", batch_size=32, learning_rate=0.1)
     p.add_argument("--graph", action="store_true", help="capture the whole step in a CUDA graph (needs equal step counts)")
     p.add_argument("--bucketMB", type=float, default=0.0, help="overlap per-bucket fused launches with backward")
+    p.add_argument("--flatOrder", choices=["module", "execution"], default="module",
+                   help="layout of the flat parameter vector ('execution': buckets are complete layer by layer)")
     p.add_argument("--conv", choices=["auto", "tc", "cudnn"], default="auto",
                    help="tc = convolutions as implicit GEMMs on the tensor cores (3xTF32, fp32-level accuracy; CUDA only), "
                         "cudnn = stock torch modules; auto = tc with --cuda")
@@ -38,7 +40,7 @@ def main(argv=None):
     data = Data(opt.nodeIndex, opt.numNodes, batch, device=dev, train_samples=opt.trainSamples, test_samples=opt.testSamples)
     use_tc = dev.type == "cuda" and opt.conv in ("auto", "tc")
     model = (cifar_convnet_tc(seed=opt.seed) if use_tc else cifar_convnet(seed=opt.seed)).to(dev)
-    flat = dl.FlatParams(comm, model, with_momentum=opt.momentum != 0)
+    flat = dl.FlatParams(comm, model, with_momentum=opt.momentum != 0, order=opt.flatOrder)
     sgd = dl.AllReduceSGD(comm, flat)
     if opt.resume:
         dl.load_checkpoint(opt.resume, flat, momentum=flat.momentum)

@@ -11,6 +11,15 @@ import torch.nn as nn
 import torch.nn.functional as F
 
 
+def _execution_order(model: nn.Module):
+    """Parameter names in the order the forward pass uses them: conv_i, bn_i, ..., linear (FlatParams(order="execution"))."""
+    names = []
+    for i in range(len(model.convs)):
+        names += [f"convs.{i}.{n}" for n, _ in model.convs[i].named_parameters()]
+        names += [f"bns.{i}.{n}" for n, _ in model.bns[i].named_parameters()]
+    return names + [f"linear.{n}" for n, _ in model.linear.named_parameters()]
+
+
 class CifarConvNet(nn.Module):
     CHANNELS = (3, 64, 128, 256, 512)
 
@@ -23,6 +32,9 @@ class CifarConvNet(nn.Module):
         self.convs = nn.ModuleList(convs)
         self.bns = nn.ModuleList(bns)
         self.linear = nn.Linear(512 * 2 * 2, 10)                   # :44-45
+
+    def execution_order(self):
+        return _execution_order(self)
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         for conv, bn in zip(self.convs, self.bns):
@@ -47,6 +59,9 @@ class CifarConvNetTC(nn.Module):
         self.bns = nn.ModuleList([FusedBNReLUPool(c, eps=1e-3) if fused_tail else nn.BatchNorm2d(c, eps=1e-3)
                                   for c in self.CHANNELS[1:]])
         self.linear = nn.Linear(512 * 2 * 2, 10)
+
+    def execution_order(self):
+        return _execution_order(self)
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         x = x.permute(0, 2, 3, 1).contiguous()                     # NCHW input batch -> NHWC once

@@ -56,15 +56,35 @@ class FlatParams:
     buffers.  ``params`` / ``grads`` (/ ``momentum``) are :class:`SymBuffer`; ``numel`` is the
     true element count and ``padded`` the allocated (32-element aligned) one.
 
-    All ranks must construct FlatParams for the same architecture in the same order."""
+    All ranks must construct FlatParams for the same architecture in the same order.
+
+    ``order`` is the layout of the flat vector: ``"module"`` (``named_parameters()`` order, what ``getParameters()``
+    gives the reference), ``"execution"`` (the order in which the forward pass uses the parameters, taken from the
+    module's ``execution_order()`` if it has one), or an explicit list of parameter names.  Execution order makes the
+    tail of the vector the first thing backward finishes, so :class:`GradBuckets` can send buckets off layer by layer;
+    in module order a bucket waits for the LAST of its tensors (e.g. every BatchNorm of a model that registers all its
+    convolutions first).  Checkpoints record the layout and are remapped by name on load."""
 
     def __init__(self, comm: Communicator, source: Union[torch.nn.Module, Iterable[torch.Tensor]],
-                 with_grads: bool = True, with_momentum: bool = False, name: str = "model"):
+                 with_grads: bool = True, with_momentum: bool = False, name: str = "model",
+                 order: Union[str, Sequence[str]] = "module"):
         self.comm = comm
         if isinstance(source, torch.nn.Module):
-            self.names = [n for n, _ in source.named_parameters()]
-            self._params: List[torch.Tensor] = [p for _, p in source.named_parameters()]
+            named = list(source.named_parameters())
+            if order == "execution":
+                order = source.execution_order() if hasattr(source, "execution_order") else "module"
+            if order != "module":
+                if isinstance(order, str):
+                    raise ValueError(f"FlatParams: unknown order {order!r}")
+                by_name = dict(named)
+                if sorted(order) != sorted(by_name):
+                    raise ValueError("FlatParams: order must list every parameter name exactly once")
+                named = [(n, by_name[n]) for n in order]
+            self.names = [n for n, _ in named]
+            self._params: List[torch.Tensor] = [p for _, p in named]
         else:
+            if order != "module":
+                raise ValueError("FlatParams: order needs a module (a list of tensors is taken as given)")
             self._params = list(source)
             self.names = [f"p{i}" for i in range(len(self._params))]
         for p in self._params:

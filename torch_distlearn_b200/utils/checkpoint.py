@@ -93,16 +93,29 @@ def load_checkpoint(path: str, flat, center: Optional[Any] = None, momentum: Opt
     """Load into the live buffers (in place, so every view stays valid); returns the header."""
     ck = read_checkpoint(path)
     hdr = ck["header"]
+    mine = [(m["name"], tuple(m["shape"]), m["offset"], m["numel"]) for m in flat.manifest()]
+    theirs = [(m["name"], tuple(m["shape"]), m["offset"], m["numel"]) for m in hdr["manifest"]]
+    same_layout = [(s, o) for _, s, o, _ in mine] == [(s, o) for _, s, o, _ in theirs]
+    permuted = not same_layout and sorted((n, s) for n, s, _, _ in mine) == sorted((n, s) for n, s, _, _ in theirs)
     if strict:
         if hdr["numel"] != flat.numel or hdr["padded"] != flat.padded:
             raise ValueError(f"checkpoint has {hdr['numel']} parameters, the model has {flat.numel}")
-        mine = [(m["name"], tuple(m["shape"])) for m in flat.manifest()]
-        theirs = [(m["name"], tuple(m["shape"])) for m in hdr["manifest"]]
-        if [s for _, s in mine] != [s for _, s in theirs]:
+        if not same_layout and not permuted:
             raise ValueError("checkpoint shape manifest does not match the model")
-    flat.params.tensor[:flat.padded].copy_(ck["params"])
+
+    def put(dst: torch.Tensor, src: torch.Tensor) -> None:
+        if not permuted:
+            dst[:flat.padded].copy_(src)
+            return
+        # same tensors, different layout of the flat vector (FlatParams(order=...)): move them one by one, by name
+        where = {n: (o, z) for n, _, o, z in theirs}
+        for n, _, o, z in mine:
+            so, sz = where[n]
+            dst[o:o + z].copy_(src[so:so + sz])
+
+    put(flat.params.tensor, ck["params"])
     if center is not None and "center" in ck:
-        _flat_of(center)[:flat.padded].copy_(ck["center"])
+        put(_flat_of(center), ck["center"])
     if momentum is not None and "momentum" in ck:
-        _flat_of(momentum)[:flat.padded].copy_(ck["momentum"])
+        put(_flat_of(momentum), ck["momentum"])
     return hdr
