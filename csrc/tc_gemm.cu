@@ -839,6 +839,8 @@ bool use_ts() {
   return v != 0;
 }
 
+#include "tc_gemm_streamk.inl"
+
 template <int BN>
 int launch(const CUtensorMap& ma, const CUtensorMap& mb, const GemmArgs& g, int splits, cudaStream_t st) {
   static bool configured[2][64] = {{false}};
@@ -860,6 +862,13 @@ int launch(const CUtensorMap& ma, const CUtensorMap& mb, const GemmArgs& g, int 
 }
 
 }  // namespace
+
+// Switch the experimental stream-K kernel on (1) or off (0) for later calls; returns the previous setting.
+extern "C" int dl_tc_gemm_streamk(int on) {
+  const int before = use_streamk() ? 1 : 0;
+  g_streamk = on ? 1 : 0;
+  return before;
+}
 
 extern "C" int dl_tc_gemm_ex(const float* A, const float* B, float* C, const float* bias, int M, int N, int K, long long lda,
                              long long ldb, long long ldc, int a_mn, int b_mn, int split_k, int accumulate, int terms,
@@ -898,6 +907,7 @@ extern "C" int dl_tc_gemm_ex(const float* A, const float* B, float* C, const flo
   if (rc != DL_OK) return rc;
   rc = b_mn ? make_map(&mb, B, K, N, ldb, BK, 1) : make_map(&mb, B, N, K, ldb, bn, 0);
   if (rc != DL_OK) return rc;
+  if (use_ts() && use_streamk()) return bn == 64 ? launch_sk<64>(ma, mb, g, accumulate, st) : launch_sk<128>(ma, mb, g, accumulate, st);
   if (splits > 1 && !accumulate) {
     // split-K partial sums are added with atomics: start from zero (row by row: C may be a strided view)
     if (ldc == N) {
@@ -965,6 +975,7 @@ extern "C" int dl_tc_conv5x5(int mode, const float* act, const float* w, float* 
   g.vec_out = (reinterpret_cast<uintptr_t>(out) % 16 == 0 && g.ldc % 4 == 0 &&
                (g.bias == nullptr || reinterpret_cast<uintptr_t>(g.bias) % 16 == 0)) ? 1 : 0;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (use_ts() && use_streamk()) return bn == 64 ? launch_sk<64>(ma, mb, g, accumulate, st) : launch_sk<128>(ma, mb, g, accumulate, st);
   if (splits > 1 && !accumulate) DL_CUDA(cudaMemsetAsync(out, 0, static_cast<size_t>(g.M) * g.N * 4, st));
   return bn == 64 ? launch<64>(ma, mb, g, splits, st) : launch<128>(ma, mb, g, splits, st);
 }

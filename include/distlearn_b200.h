@@ -186,6 +186,12 @@ int dl_tc_gemm_ex(const float* A, const float* B, float* C, const float* bias, i
 int dl_tc_conv5x5(int mode, const float* act, const float* w, float* out, const float* bias, int B, int H, int W,
                   int Cin, int Cout, int split_k, int accumulate, int terms, void* stream);
 
+/* EXPERIMENTAL (not yet validated on a GPU): stream-K form of the tensor-core GEMM — one persistent CTA per SM takes a
+ * contiguous range of (tile, K-block) units, so 256 tiles on 148 SMs cost 86.5 K-block times instead of 100
+ * (csrc/tc_gemm_streamk.inl).  on = 1 / 0 switches it for later dl_tc_gemm* / dl_tc_conv5x5 calls (initial value:
+ * environment variable DL_B200_TC_STREAMK, default 0); returns the previous setting. */
+int dl_tc_gemm_streamk(int on);
+
 /* 5x5 / stride 1 / pad 2 convolution pieces on NHWC activations (SpatialConvolutionMM = im2col + GEMM,
  * examples/Model.lua:20-38): col[B*H*W, ld] with columns ordered (kh, kw, cin); col2im sums the 25 taps
  * back into dx[B,H,W,C]. */
