@@ -281,6 +281,7 @@ int dlh_open(const char* name, int rank, int world, uint64_t heap_bytes, double 
     while (hdr->attached.load(std::memory_order_acquire) < static_cast<uint32_t>(world)) {
       if (now_s() - t0 > limit) {
         set_error("timed out waiting for all %d ranks to attach to '%s'", world, name);
+        if (rank == 0) shm_unlink(name);
         munmap(map, total);
         delete h;
         return DL_ETIMEOUT;
@@ -288,6 +289,9 @@ int dlh_open(const char* name, int rank, int world, uint64_t heap_bytes, double 
       usleep(500);
     }
   }
+  // Every rank holds a mapping now, so the NAME is no longer needed: drop it here rather than at close, and a job that
+  // is killed later leaves nothing behind in /dev/shm.
+  if (rank == 0) shm_unlink(name);
   *out = h;
   return DL_OK;
 }
