@@ -151,6 +151,17 @@ def host():
     _sig(lib, "dlh_mailbox_write", i32, [vp, i32, i32, u64])
     _sig(lib, "dlh_mailbox_read", i32, [vp, i32, i32, P(u64)])
     _sig(lib, "dlh_peer_pull", i32, [vp, i32, u64, vp, u64])
+    # native batch loader (csrc/loader.cpp)
+    i64 = C.c_int64
+    _sig(lib, "dll_last_error", C.c_char_p, [])
+    _sig(lib, "dll_create", i32, [vp, i32, vp, i64, i32, i32, vp, vp, i32, i32, i32, i32, i32, u64, i32, i32, P(vp), P(vp), P(vp)])
+    _sig(lib, "dll_next", i32, [vp, P(i32), P(i32), P(i64), C.c_double])
+    _sig(lib, "dll_release", i32, [vp])
+    _sig(lib, "dll_num_batches", i64, [vp])
+    _sig(lib, "dll_num_samples", i64, [vp])
+    _sig(lib, "dll_samples_done", u64, [vp])
+    _sig(lib, "dll_destroy", i32, [vp])
+    _sig(lib, "dll_read_cifar_bin", i64, [C.c_char_p, vp, vp, i64])
     return lib
 
 

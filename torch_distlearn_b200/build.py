@@ -38,7 +38,7 @@ CUDA_SOURCES = [
     "bn_ops.cu",
     "head_ops.cu",
 ]
-HOST_SOURCES = ["host_transport.cpp"]
+HOST_SOURCES = ["host_transport.cpp", "loader.cpp"]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",

@@ -5,3 +5,4 @@ from .color_print import print_client, print_server
 from .data import Batch, Data, SyntheticDataset, cifar_dataset, mnist_dataset
 from .logging import Logger, RankLogger
 from .metrics import ConfusionMatrix
+from .native_loader import NativeBatcher, read_cifar10_bin

@@ -103,6 +103,31 @@ class SyntheticDataset:
 
     sampled_batcher = sampledBatcher
 
+    # ---- native path: the partition materialised once as bytes, batches assembled by C++ threads ----------------
+    U8_RANGE = 8.0      # samples are prototype (~N(0,1)) + noise: [-4, 4) covers them; quantisation step 1/32
+
+    def materialize_u8(self) -> torch.Tensor:
+        """Every sample of this partition as uint8 ``[n, *input_dims]`` (what a dataset on disk looks like):
+        ``x = u8 * (U8_RANGE / 255) - U8_RANGE / 2`` gives the float sample back to within one quantisation step."""
+        gen = torch.Generator().manual_seed(self.seed + 17)
+        n = len(self)
+        out = torch.empty((n,) + self.input_dims, dtype=torch.uint8)
+        for lo in range(0, n, 4096):                      # bounded temporaries
+            idx = torch.arange(lo, min(lo + 4096, n))
+            x, _ = self.materialize(idx, gen)
+            out[lo:lo + len(idx)] = ((x / self.U8_RANGE + 0.5) * 255).round().clamp_(0, 255).to(torch.uint8)
+        return out
+
+    def nativeBatcher(self, batchSize: int, samplerKind: str = "permutation", threads: int = 2, depth: int = 4, **kw):
+        """A :class:`~torch_distlearn_b200.utils.native_loader.NativeBatcher` over this partition (csrc/loader.cpp): the
+        Python batcher above costs ~5 ms per 128-sample CIFAR batch (`profiles/loader_cpu.jsonl`), several GPU steps."""
+        from .native_loader import NativeBatcher
+        if not hasattr(self, "_u8"):
+            self._u8 = self.materialize_u8()
+        return NativeBatcher(self._u8, self.labels, batchSize, sampler=samplerKind, num_classes=self.num_classes,
+                             scale=self.U8_RANGE / 255, mean=[self.U8_RANGE / 2], std=[1.0], seed=self.seed, threads=threads,
+                             depth=depth, **kw)
+
 
 def mnist_dataset(partition: int = 1, partitions: int = 1, num_samples: int = 60000, seed: int = 1) -> SyntheticDataset:
     """MNIST-shaped: 1024-vectors (32x32 padded digits, examples/mnist.lua:34,53)."""
@@ -119,10 +144,25 @@ class Data:
     getTestBatch, numTestBatches, classes  (examples/Data.lua:5-74)."""
 
     def __init__(self, partitionNum: int, partitions: int, batchSize: int, cuda: bool = False, train_samples: int = 50000,
-                 test_samples: int = 10000, device: Optional[torch.device] = None):
+                 test_samples: int = 10000, device: Optional[torch.device] = None, native: bool = True, threads: int = 2):
         self.train = cifar_dataset(partitionNum, partitions, train_samples, seed=2)
         self.test = cifar_dataset(partitionNum, partitions, test_samples, seed=3)
         self.test.prototypes = self.train.prototypes  # same distribution
-        self.getTrainingBatch, self.numTrainingBatches = self.train.sampledBatcher(batchSize, "label-uniform", cuda, device)
-        self.getTestBatch, self.numTestBatches = self.test.sampledBatcher(batchSize, "permutation", cuda, device)
         self.classes = list(CIFAR_CLASSES)
+        self._native = []
+        if native:
+            # batches come from C++ worker threads, already normalised, in pinned memory (utils/native_loader.py)
+            dev = device if device is not None else (torch.device("cuda") if cuda else torch.device("cpu"))
+            tr = self.train.nativeBatcher(batchSize, "label-uniform", threads=threads)
+            te = self.test.nativeBatcher(batchSize, "permutation", threads=1)
+            self._native = [tr, te]
+            self.getTrainingBatch, self.numTrainingBatches = tr.sampledBatcher(dev)
+            self.getTestBatch, self.numTestBatches = te.sampledBatcher(dev)
+        else:
+            self.getTrainingBatch, self.numTrainingBatches = self.train.sampledBatcher(batchSize, "label-uniform", cuda, device)
+            self.getTestBatch, self.numTestBatches = self.test.sampledBatcher(batchSize, "permutation", cuda, device)
+
+    def close(self) -> None:
+        for nb in self._native:
+            nb.close()
+        self._native = []
