@@ -37,7 +37,8 @@ def main(argv=None):
     comm, log = setup(opt)
     dev = comm.device
     batch = math.ceil(opt.batchSize / opt.numNodes)                 # examples/cifar10.lua:36
-    data = Data(opt.nodeIndex, opt.numNodes, batch, device=dev, train_samples=opt.trainSamples, test_samples=opt.testSamples)
+    data = Data(opt.nodeIndex, opt.numNodes, batch, device=dev, train_samples=opt.trainSamples, test_samples=opt.testSamples,
+                native=not opt.pythonLoader, threads=opt.loaderThreads)
     use_tc = dev.type == "cuda" and opt.conv in ("auto", "tc")
     model = (cifar_convnet_tc(seed=opt.seed) if use_tc else cifar_convnet(seed=opt.seed)).to(dev)
     flat = dl.FlatParams(comm, model, with_momentum=opt.momentum != 0, order=opt.flatOrder)

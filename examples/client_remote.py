@@ -33,7 +33,8 @@ def main(argv=None):
     comm, log = setup(opt)
     dev = comm.device
     batch = math.ceil(opt.batchSize / opt.numNodes)
-    data = Data(opt.nodeIndex, opt.numNodes, batch, device=dev, train_samples=opt.trainSamples, test_samples=opt.testSamples)
+    data = Data(opt.nodeIndex, opt.numNodes, batch, device=dev, train_samples=opt.trainSamples, test_samples=opt.testSamples,
+                native=not opt.pythonLoader, threads=opt.loaderThreads)
     model = cifar_convnet(seed=opt.seed).to(dev)
     flat = dl.FlatParams(comm, model)
     ea = dl.AllReduceEA(comm, opt.tau, opt.alpha, flat=flat)

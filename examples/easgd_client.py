@@ -26,7 +26,8 @@ def main(argv=None):
     comm, log = setup(opt, rank=opt.nodeIndex, world=world)          # client i is rank i (the server is rank 0)
     dev = comm.device
     data = Data(opt.nodeIndex, opt.numNodes, opt.batchSize, device=dev, train_samples=opt.trainSamples,
-                test_samples=opt.testSamples)                        # partitioned over the clients (:75)
+                test_samples=opt.testSamples,
+                native=not opt.pythonLoader, threads=opt.loaderThreads)                        # partitioned over the clients (:75)
     model = cifar_convnet(seed=opt.seed).to(dev)
     flat = dl.FlatParams(comm, model)
     algo = dl.AsyncEA(comm, "client", opt.communicationTime, opt.alpha, server_rank=server_rank,

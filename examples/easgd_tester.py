@@ -23,7 +23,8 @@ def main(argv=None):
     world, server_rank, tester_rank = easgd_topology(opt)
     comm, log = setup(opt, rank=tester_rank, world=world, loud=True)
     dev = comm.device
-    data = Data(1, 1, opt.batchSize, device=dev, train_samples=opt.trainSamples, test_samples=opt.testSamples)   # full data (:75)
+    data = Data(1, 1, opt.batchSize, device=dev, train_samples=opt.trainSamples, test_samples=opt.testSamples,
+                native=not opt.pythonLoader, threads=opt.loaderThreads)   # full data (:75)
     model = cifar_convnet(seed=opt.seed).to(dev)
     flat = dl.FlatParams(comm, model)          # same allocation sequence on every rank: the heap is symmetric
     algo = dl.AsyncEA(comm, "tester", opt.communicationTime, opt.alpha, server_rank=server_rank,

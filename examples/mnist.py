@@ -31,7 +31,10 @@ def main(argv=None):
     dev = comm.device
     # partition the data over the nodes (examples/mnist.lua:26-29)
     ds = mnist_dataset(opt.nodeIndex, opt.numNodes, opt.trainSamples, seed=1)
-    get_batch, num_batches = ds.sampledBatcher(opt.batchSize, "permutation", device=dev)
+    if opt.pythonLoader:
+        get_batch, num_batches = ds.sampledBatcher(opt.batchSize, "permutation", device=dev)
+    else:       # C++ worker threads fill pinned batches ahead of the step (utils/native_loader.py)
+        get_batch, num_batches = ds.nativeBatcher(opt.batchSize, "permutation", threads=opt.loaderThreads).sampledBatcher(dev)
     model = mnist_convnet(seed=opt.seed).to(dev)
     flat = dl.FlatParams(comm, model, with_momentum=opt.momentum != 0)
     sgd = dl.AllReduceSGD(comm, flat)

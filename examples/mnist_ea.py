@@ -24,7 +24,10 @@ def main(argv=None):
     comm, log = setup(opt)
     dev = comm.device
     ds = mnist_dataset(opt.nodeIndex, opt.numNodes, opt.trainSamples, seed=1)
-    get_batch, num_batches = ds.sampledBatcher(opt.batchSize, "permutation", device=dev)
+    if opt.pythonLoader:
+        get_batch, num_batches = ds.sampledBatcher(opt.batchSize, "permutation", device=dev)
+    else:       # C++ worker threads fill pinned batches ahead of the step (utils/native_loader.py)
+        get_batch, num_batches = ds.nativeBatcher(opt.batchSize, "permutation", threads=opt.loaderThreads).sampledBatcher(dev)
     model = mnist_convnet(seed=opt.seed + opt.nodeIndex).to(dev)   # nodes start apart; the initial sync aligns them
     flat = dl.FlatParams(comm, model, with_momentum=opt.momentum != 0)
     ea = dl.AllReduceEA(comm, opt.tau, opt.alpha, flat=flat)

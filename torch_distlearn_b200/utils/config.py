@@ -44,6 +44,9 @@ def base_parser(description: str, batch_size: int = 32, learning_rate: float = 0
     p.add_argument("--metrics", type=str, default="", help="JSONL metrics file (node 1)")
     p.add_argument("--verbose", action="store_true", help="protocol tracing")
     p.add_argument("--seed", type=int, default=0)
+    p.add_argument("--pythonLoader", action="store_true",
+                   help="assemble batches in Python instead of the native loader threads (csrc/loader.cpp)")
+    p.add_argument("--loaderThreads", type=int, default=2, help="worker threads of the native batch loader")
     return p
 
 
