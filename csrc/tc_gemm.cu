@@ -870,6 +870,29 @@ extern "C" int dl_tc_gemm_streamk(int on) {
   return before;
 }
 
+// The stream-K work list of CTA `cta` for an M x N x K problem on `sms` SMs, computed by the same functions the kernel
+// uses (host-side check of the decomposition; no GPU needed).  Writes up to `max_segments` rows of
+// (m0, n0, first K block, K blocks) into `segments`; returns the number of segments of that CTA, *grid = CTAs launched.
+extern "C" int dl_tc_streamk_plan(int M, int N, int K, int sms, int cta, int* grid, int* segments, int max_segments) {
+  DL_REQUIRE(M > 0 && N > 0 && K > 0 && sms > 0 && grid != nullptr, "dl_tc_streamk_plan: bad arguments");
+  const int bn = N <= 64 ? 64 : 128;
+  long long gsz = 0;
+  const SkArgs k = sk_plan(M, N, K, bn, sms, &gsz);
+  *grid = static_cast<int>(gsz);
+  DL_REQUIRE(cta >= 0 && cta < gsz, "dl_tc_streamk_plan: CTA %d outside the grid of %lld", cta, gsz);
+  const long long u_begin = k.units * cta / gsz, u_end = k.units * (cta + 1) / gsz;
+  int n = 0;
+  for (long long u = u_begin; u < u_end;) {
+    const SkSegment sg = sk_segment(k, u, u_end, bn);
+    if (segments != nullptr && n < max_segments) {
+      segments[4 * n + 0] = sg.m0; segments[4 * n + 1] = sg.n0; segments[4 * n + 2] = sg.kb0; segments[4 * n + 3] = sg.nkb;
+    }
+    ++n;
+    u += sg.nkb;
+  }
+  return n;
+}
+
 extern "C" int dl_tc_gemm_ex(const float* A, const float* B, float* C, const float* bias, int M, int N, int K, long long lda,
                              long long ldb, long long ldc, int a_mn, int b_mn, int split_k, int accumulate, int terms,
                              void* stream) {

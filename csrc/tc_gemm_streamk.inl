@@ -24,7 +24,7 @@ struct SkSegment {
 };
 
 // the segment that starts at unit u of a range ending at u_end
-__device__ __forceinline__ SkSegment sk_segment(const SkArgs& k, long long u, long long u_end, int bn) {
+__host__ __device__ __forceinline__ SkSegment sk_segment(const SkArgs& k, long long u, long long u_end, int bn) {
   SkSegment s;
   const long long tile = u / k.total_kb;
   s.kb0 = static_cast<int>(u - tile * k.total_kb);
@@ -319,6 +319,20 @@ bool use_streamk() {
   return g_streamk != 0;
 }
 
+// Work decomposition for an M x N x K problem on `sms` SMs: one CTA per SM (512 TMEM columns and ~200 KB of shared
+// memory each), never fewer than 4 K blocks per CTA.
+SkArgs sk_plan(int M, int N, int K, int bn, int sms, long long* grid) {
+  SkArgs k;
+  k.m_tiles = (M + BM - 1) / BM;
+  k.n_tiles = (N + bn - 1) / bn;
+  k.total_kb = (K + BK - 1) / BK;
+  k.units = static_cast<long long>(k.m_tiles) * k.n_tiles * k.total_kb;
+  long long gsz = sms;
+  if (gsz > k.units / 4) gsz = k.units / 4 > 0 ? k.units / 4 : 1;
+  *grid = gsz;
+  return k;
+}
+
 // `accumulate`: C already holds values to add to (every segment uses red.add, nothing is zeroed)
 template <int BN>
 int launch_sk(const CUtensorMap& ma, const CUtensorMap& mb, GemmArgs g, int accumulate, cudaStream_t st) {
@@ -333,15 +347,9 @@ int launch_sk(const CUtensorMap& ma, const CUtensorMap& mb, GemmArgs g, int accu
     DL_CUDA(cudaDeviceGetAttribute(&sm_count[dev], cudaDevAttrMultiProcessorCount, dev));
     configured[dev] = true;
   }
-  SkArgs k;
-  k.m_tiles = (g.M + BM - 1) / BM;
-  k.n_tiles = (g.N + BN - 1) / BN;
-  k.total_kb = (g.K + BK - 1) / BK;
-  k.units = static_cast<long long>(k.m_tiles) * k.n_tiles * k.total_kb;
+  long long grid = 0;
+  const SkArgs k = sk_plan(g.M, g.N, g.K, BN, sm_count[dev] > 0 ? sm_count[dev] : 148, &grid);
   const long long tiles = static_cast<long long>(k.m_tiles) * k.n_tiles;
-  // one CTA per SM (512 TMEM columns and ~200 KB of shared memory each); never fewer than 4 K blocks per CTA
-  long long grid = sm_count[dev] > 0 ? sm_count[dev] : 148;
-  if (grid > k.units / 4) grid = k.units / 4 > 0 ? k.units / 4 : 1;
   g.atomic_out = accumulate ? 1 : 0;
   g.kblocks_per_split = k.total_kb;
   if (!accumulate && tiles % grid != 0) {

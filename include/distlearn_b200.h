@@ -191,6 +191,9 @@ int dl_tc_conv5x5(int mode, const float* act, const float* w, float* out, const 
  * (csrc/tc_gemm_streamk.inl).  on = 1 / 0 switches it for later dl_tc_gemm* / dl_tc_conv5x5 calls (initial value:
  * environment variable DL_B200_TC_STREAMK, default 0); returns the previous setting. */
 int dl_tc_gemm_streamk(int on);
+/* Host-side view of the stream-K decomposition (same code as the kernel): the segments (m0, n0, first K block, K blocks)
+ * of CTA `cta`; returns their number, *grid = CTAs the launch would use on `sms` SMs. */
+int dl_tc_streamk_plan(int M, int N, int K, int sms, int cta, int* grid, int* segments, int max_segments);
 
 /* 5x5 / stride 1 / pad 2 convolution pieces on NHWC activations (SpatialConvolutionMM = im2col + GEMM,
  * examples/Model.lua:20-38): col[B*H*W, ld] with columns ordered (kh, kw, cin); col2im sums the 25 taps
