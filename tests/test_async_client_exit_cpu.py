@@ -1,0 +1,59 @@
+"""AsyncEA tolerates a client that disappears ("tolerates client exit by construction"): syncs need no
+handshake with the server, so the survivors keep exchanging with the center, the server keeps seeing their syncs, and
+what the server gets when NOBODY is left is a TimeoutError instead of the reference's eternal recvAny()."""
+import pytest
+import torch
+
+from mp_util import run_ranks
+
+
+def _w_client_exit(rank, world, job):
+    import torch_distlearn_b200 as dl
+    from torch_distlearn_b200.parallel.async_ea import AsyncEA
+    comm = dl.HostCommunicator(rank, world, name=job, heap_mb=4, timeout_s=30)
+    n, tau, alpha = 40, 2, 0.25
+    out = {}
+    if rank == 0:
+        srv = AsyncEA(comm, "server", tau, alpha, server_rank=0, num_clients=world - 1)
+        p = [torch.full((n,), 100.0)]
+        srv.initServer(p)
+        seen = 0
+        timed_out = False
+        while True:
+            try:
+                if not srv.syncServer(p, timeout=3.0):
+                    break
+                seen = srv.syncs
+            except TimeoutError:
+                timed_out = True          # one client never said finish(): the server is told by the clock, not hung
+                break
+        out = {"role": "server", "syncs": seen, "timed_out": timed_out, "center": p[0].clone()}
+    else:
+        cl = AsyncEA(comm, "client", tau, alpha, server_rank=0, num_clients=world - 1)
+        p = [torch.zeros(n)]
+        cl.initClient(p)
+        steps = 2 if rank == 1 else 8       # rank 1 "dies" after one sync and never calls finish()
+        synced = 0
+        for _ in range(steps):
+            p[0].add_(1.0)
+            synced += int(cl.syncClient(p))
+        if rank != 1:
+            cl.finish()
+        out = {"role": "client", "synced": synced, "w": p[0].clone()}
+    import time
+    time.sleep(4.0 if rank != 0 else 0.0)    # keep the mapping alive until the server has noticed
+    comm.close()
+    return out
+
+
+@pytest.mark.timeout(120)
+def test_server_and_survivors_outlive_a_client_that_vanishes():
+    res = run_ranks(_w_client_exit, 3, timeout=90)
+    server, dead, alive = res
+    assert dead["synced"] == 1 and alive["synced"] == 4
+    assert server["syncs"] == 5                       # every sync that happened was seen
+    assert server["timed_out"] is True                # and the missing finish() ended in a timeout, not a hang
+    # conservation still holds over everything that was exchanged
+    total = server["center"].double() + dead["w"].double() + alive["w"].double()
+    want = 100.0 + (100.0 + 2) + (100.0 + 8)
+    torch.testing.assert_close(total, torch.full((40,), want, dtype=torch.float64), rtol=1e-5, atol=1e-4)
