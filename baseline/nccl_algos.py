@@ -9,7 +9,7 @@ They mirror the reference's dataflow with library collectives:
 """
 from __future__ import annotations
 
-from typing import Iterable, List, Optional
+from typing import Iterable, Optional
 
 import torch
 import torch.distributed as dist

@@ -6,8 +6,6 @@ Loop order is the reference's (examples/EASGD_client.lua:106-117): gradient at x
 d = alpha (x - c), x -= d locally and adds d into the center with NVLink atomics), then the SGD step
 with the gradient computed before the sync.
 """
-import math
-
 from common import batches_this_epoch, easgd_topology, forward_backward, setup, Throughput
 
 import torch

@@ -10,7 +10,6 @@ import torch
 import torch_distlearn_b200 as dl
 from torch_distlearn_b200.models import cifar_convnet_tc
 from torch_distlearn_b200.ops import bn as bn_ops
-from torch_distlearn_b200.parallel import bucketed
 from torch_distlearn_b200.parallel.trainer import TrainStep
 
 DEV = "cuda:0"

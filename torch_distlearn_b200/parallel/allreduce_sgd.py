@@ -26,9 +26,7 @@ from __future__ import annotations
 
 from typing import Any, Optional
 
-import torch
-
-from .comm import Communicator, SymBuffer
+from .comm import Communicator
 from .flat import FlatParams, TableStager
 
 

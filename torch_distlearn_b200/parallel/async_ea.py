@@ -36,7 +36,7 @@ from typing import Any, Optional
 import torch
 
 from .comm import Communicator, SymBuffer
-from .flat import FlatParams, TableStager, walk_table
+from .flat import FlatParams, walk_table
 
 # mailbox words in the SERVER's pad
 MB_READY, MB_TEST_SEQ, MB_TEST_ACK, MB_STOP = 0, 1, 2, 3

@@ -12,7 +12,7 @@ the same sequence of collective kernels.  The whole fork/join pattern is captura
 """
 from __future__ import annotations
 
-from typing import List, Optional
+from typing import List
 
 import torch
 

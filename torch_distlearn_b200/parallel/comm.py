@@ -23,7 +23,7 @@ import os
 import threading
 import uuid
 from dataclasses import dataclass
-from typing import List, Optional, Sequence
+from typing import List, Optional
 
 import torch
 

@@ -34,7 +34,6 @@ class ConfusionMatrix:
     def batchAdd(self, predictions: torch.Tensor, targets: torch.Tensor) -> None:
         """A batch of score rows [B, C] and targets [B]; on CUDA this is one kernel launch."""
         if predictions.is_cuda and self.mat.is_cuda and predictions.dtype == torch.float32 and predictions.is_contiguous():
-            import ctypes as C
             from .. import _lib
             lib = _lib.cuda()
             t = targets.to(torch.int64).contiguous()
