@@ -17,6 +17,8 @@ from .parallel.allreduce_sgd import AllReduceSGD
 from .parallel.allreduce_ea import AllReduceEA
 from .parallel.async_ea import AsyncEA
 from .parallel.tree import LocalhostTree, Tree
+from .parallel.trainer import TrainStep
+from .parallel.bucketed import GradBuckets
 from .utils.checkpoint import load_checkpoint, save_checkpoint
 from .utils.color_print import print_client, print_server
 
@@ -25,5 +27,13 @@ __version__ = "0.1.0"
 __all__ = [
     "CommResult", "Communicator", "DistCommunicator", "EmulatedCommunicator", "HostCommunicator", "P2PCommunicator", "SymBuffer",
     "create_communicator", "FlatParams", "TableStager", "walk_table", "AllReduceSGD", "AllReduceEA", "AsyncEA",
-    "LocalhostTree", "Tree", "save_checkpoint", "load_checkpoint", "print_client", "print_server",
+    "LocalhostTree", "Tree", "TrainStep", "GradBuckets", "make_communicator", "save_checkpoint", "load_checkpoint", "print_client", "print_server",
 ]
+
+
+def __getattr__(name):
+    # lazy: importing .launch here would shadow `python -m torch_distlearn_b200.launch`
+    if name == "make_communicator":
+        from .launch import make_communicator
+        return make_communicator
+    raise AttributeError(f"module {__name__!r} has no attribute {name!r}")
