@@ -167,6 +167,66 @@ int check(Handle* h, int ch) {
   return DL_OK;
 }
 
+// ---- blocked, branch-free inner loops for the float paths -----------------------------------------------------------
+// The slice is walked in blocks that stay in L1: the active ranks' vectors are summed into a local buffer IN RANK ORDER
+// (the same order as the scalar code they replace and as the GPU kernels, so results do not depend on which path ran),
+// the update runs on the buffer, and the result is copied out to every rank.  Each loop is a plain a[i] op b[i] over
+// restrict pointers, which g++ vectorises; DLH_CLONES adds an AVX2 copy picked at load time.  Built with
+// -ffp-contract=off: no fused multiply-adds, the rounding is the one written here.
+#if defined(__x86_64__) && defined(__GNUC__) && !defined(__clang__)
+#define DLH_CLONES __attribute__((target_clones("avx2", "default")))
+#else
+#define DLH_CLONES
+#endif
+constexpr uint64_t kBlock = 2048;
+
+DLH_CLONES void blk_add(float* __restrict acc, const float* __restrict src, uint64_t len) {
+  for (uint64_t i = 0; i < len; ++i) acc[i] += src[i];
+}
+DLH_CLONES void blk_scale(float* __restrict acc, float f, uint64_t len) {
+  for (uint64_t i = 0; i < len; ++i) acc[i] *= f;
+}
+// acc <- sum over the active ranks (ascending) of src[r][0..len)
+void blk_sum_active(float* acc, const float* const* src, int world, uint32_t mask, uint64_t len) {
+  if (mask & 1u) memcpy(acc, src[0], len * sizeof(float));
+  else memset(acc, 0, len * sizeof(float));
+  for (int r = 1; r < world; ++r)
+    if ((mask >> r) & 1u) blk_add(acc, src[r], len);
+}
+// g (summed gradients, in) -> new parameters (out), exactly: g*=inv; g+=wd*p; m=mom*m+g; g=nesterov? g+mom*m : m; p-=lr*g
+DLH_CLONES void blk_sgd_plain(float* __restrict g, const float* __restrict p, float inv, float wd, float lr, uint64_t len) {
+  if (wd != 0.f) {
+    for (uint64_t i = 0; i < len; ++i) {
+      const float gi = g[i] * inv + wd * p[i];
+      g[i] = p[i] - lr * gi;
+    }
+  } else {
+    for (uint64_t i = 0; i < len; ++i) g[i] = p[i] - lr * (g[i] * inv);
+  }
+}
+DLH_CLONES void blk_sgd_momentum(float* __restrict g, const float* __restrict p, float* __restrict m, float inv, float wd,
+                                 float lr, float momentum, int nesterov, uint64_t len) {
+  for (uint64_t i = 0; i < len; ++i) {
+    float gi = g[i] * inv;
+    if (wd != 0.f) gi += wd * p[i];
+    const float mi = momentum * m[i] + gi;
+    m[i] = mi;
+    gi = nesterov ? gi + momentum * mi : mi;
+    g[i] = p[i] - lr * gi;
+  }
+}
+// acc <- c + sum_r (x_r - c) * alpha   (ranks ascending, starting from 0.f like the scalar form)
+DLH_CLONES void blk_ea_accumulate(float* __restrict sum, const float* __restrict x, const float* __restrict c, float alpha,
+                                  uint64_t len) {
+  for (uint64_t i = 0; i < len; ++i) sum[i] += (x[i] - c[i]) * alpha;
+}
+DLH_CLONES void blk_add_to(float* __restrict out, const float* __restrict a, const float* __restrict b, uint64_t len) {
+  for (uint64_t i = 0; i < len; ++i) out[i] = a[i] + b[i];
+}
+DLH_CLONES void blk_ea_local(float* __restrict x, const float* __restrict c, float alpha, uint64_t len) {
+  for (uint64_t i = 0; i < len; ++i) x[i] -= (x[i] - c[i]) * alpha;
+}
+
 template <typename T>
 void reduce_typed(Handle* h, uint64_t off, uint64_t n, uint32_t mask, bool scale, int n_act) {
   // owner-computes over this rank's slice, push to everyone (same as the two-shot GPU kernel)
@@ -188,11 +248,17 @@ template <>
 void reduce_typed<float>(Handle* h, uint64_t off, uint64_t n, uint32_t mask, bool scale, int n_act) {
   const Slice s = slice_of(n, h->rank, h->world);
   const float inv = (scale && n_act > 1) ? 1.f / static_cast<float>(n_act) : 1.f;
-  for (uint64_t i = s.begin; i < s.end; ++i) {
-    float acc = (mask & 1u) ? h->at<float>(0, off)[i] : 0.f;
-    for (int r = 1; r < h->world; ++r) acc += ((mask >> r) & 1u) ? h->at<float>(r, off)[i] : 0.f;
-    acc *= inv;
-    for (int r = 0; r < h->world; ++r) h->at<float>(r, off)[i] = acc;
+  const float* src[DL_MAX_RANKS];
+  float* dst[DL_MAX_RANKS];
+  for (int r = 0; r < h->world; ++r) src[r] = dst[r] = h->at<float>(r, off);
+  alignas(64) float acc[kBlock];
+  for (uint64_t b0 = s.begin; b0 < s.end; b0 += kBlock) {
+    const uint64_t len = s.end - b0 < kBlock ? s.end - b0 : kBlock;
+    const float* blk[DL_MAX_RANKS];
+    for (int r = 0; r < h->world; ++r) blk[r] = src[r] + b0;
+    blk_sum_active(acc, blk, h->world, mask, len);
+    blk_scale(acc, inv, len);
+    for (int r = 0; r < h->world; ++r) memcpy(dst[r] + b0, acc, len * sizeof(float));
   }
 }
 
@@ -374,19 +440,21 @@ int dlh_fused_sgd(void* handle, uint64_t g_off, uint64_t p_off, uint64_t m_off, 
     const float inv = n_act > 1 ? 1.f / static_cast<float>(n_act) : 1.f;
     float* p_loc = h->at<float>(h->rank, p_off);
     float* m_loc = m_off ? h->at<float>(h->rank, m_off) : nullptr;
-    for (uint64_t i = s.begin; i < s.end; ++i) {
-      float acc = (mask & 1u) ? h->at<float>(0, g_off)[i] : 0.f;
-      for (int r = 1; r < h->world; ++r) acc += ((mask >> r) & 1u) ? h->at<float>(r, g_off)[i] : 0.f;
-      float g = acc * inv;
-      float p = p_loc[i];
-      if (wd != 0.f) g += wd * p;
-      if (m_loc) {
-        const float m = momentum * m_loc[i] + g;
-        m_loc[i] = m;
-        g = nesterov ? g + momentum * m : m;
-      }
-      p -= lr * g;
-      for (int r = 0; r < h->world; ++r) h->at<float>(r, p_off)[i] = p;
+    const float* g_src[DL_MAX_RANKS];
+    float* p_dst[DL_MAX_RANKS];
+    for (int r = 0; r < h->world; ++r) {
+      g_src[r] = h->at<float>(r, g_off);
+      p_dst[r] = h->at<float>(r, p_off);
+    }
+    alignas(64) float acc[kBlock];
+    for (uint64_t b0 = s.begin; b0 < s.end; b0 += kBlock) {
+      const uint64_t len = s.end - b0 < kBlock ? s.end - b0 : kBlock;
+      const float* blk[DL_MAX_RANKS];
+      for (int r = 0; r < h->world; ++r) blk[r] = g_src[r] + b0;
+      blk_sum_active(acc, blk, h->world, mask, len);
+      if (m_loc) blk_sgd_momentum(acc, p_loc + b0, m_loc + b0, inv, wd, lr, momentum, nesterov, len);
+      else blk_sgd_plain(acc, p_loc + b0, inv, wd, lr, len);
+      for (int r = 0; r < h->world; ++r) memcpy(p_dst[r] + b0, acc, len * sizeof(float));
     }
   }
   rc = barrier(h, channel, 0u, nullptr);
@@ -412,19 +480,21 @@ int dlh_fused_ea(void* handle, uint64_t x_off, uint64_t c_off, uint64_t cnew_off
   const float* c_old = h->at<float>(h->rank, c_off);
   if (n_act > 0) {
     const Slice s = slice_of(n, h->rank, h->world);
-    for (uint64_t i = s.begin; i < s.end; ++i) {
-      const float cv = c_old[i];
-      float sum = 0.f;
-      for (int r = 0; r < h->world; ++r) sum += (h->at<float>(r, x_off)[i] - cv) * alpha;
-      const float cn = cv + sum;
-      for (int r = 0; r < h->world; ++r) h->at<float>(r, cnew_off)[i] = cn;
+    alignas(64) float sum[kBlock];
+    alignas(64) float cn[kBlock];
+    for (uint64_t b0 = s.begin; b0 < s.end; b0 += kBlock) {
+      const uint64_t len = s.end - b0 < kBlock ? s.end - b0 : kBlock;
+      memset(sum, 0, len * sizeof(float));
+      for (int r = 0; r < h->world; ++r) blk_ea_accumulate(sum, h->at<float>(r, x_off) + b0, c_old + b0, alpha, len);
+      blk_add_to(cn, c_old + b0, sum, len);
+      for (int r = 0; r < h->world; ++r) memcpy(h->at<float>(r, cnew_off) + b0, cn, len * sizeof(float));
     }
   }
   rc = barrier(h, channel, 0u, nullptr);
   if (rc) return rc;
   if (n_act > 0) {
     float* x = h->at<float>(h->rank, x_off);
-    for (uint64_t i = 0; i < n; ++i) x[i] -= (x[i] - c_old[i]) * alpha;
+    blk_ea_local(x, c_old, alpha, n);
   } else {
     memcpy(h->at<float>(h->rank, cnew_off), c_old, n * sizeof(float));
   }
