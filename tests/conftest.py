@@ -12,6 +12,7 @@ for p in (ROOT, os.path.join(ROOT, "tests")):
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box with -m gpu)")
     config.addinivalue_line("markers", "multigpu: needs >= 2 CUDA devices")
+    config.addinivalue_line("markers", "timeout(seconds): per-test limit (pytest-timeout; a plain label without the plugin)")
 
 
 def pytest_collection_modifyitems(config, items):
