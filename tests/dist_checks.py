@@ -278,6 +278,43 @@ def verify_sgd_bucketed(results, world, **_kw) -> None:
     assert torch.isfinite(results[0]["whole"]).all()
 
 
+
+# ---- table API, one node with an empty partition (no initial synchronizeParameters) ---------------------------
+def run_sgd_table_empty_partition(comm, rank, world, steps0=2) -> Dict[str, Any]:
+    """Rank `world-1` takes no step at all and goes straight to synchronizeParameters with a plain table; the others
+    stage gradients first.  Staging buffers must land at the same heap offsets on every rank regardless."""
+    import torch_distlearn_b200 as dl
+    sgd = dl.AllReduceSGD(comm)
+    dev = _dev(comm)
+    params = [torch.full((5,), 2.0 + rank).to(dev), torch.full((3, 2), -1.0 - rank).to(dev)]
+    grads = [torch.zeros(5, device=dev), torch.zeros(3, 2, device=dev)]
+    steps = 0 if rank == world - 1 else steps0 + rank
+    for s in range(steps):
+        for g in grads:
+            g.fill_(0.1 * (s + 1))
+        sgd.sumAndNormalizeGradients(grads)
+        for p, g in zip(params, grads):
+            p.sub_(g)
+    winner = sgd.synchronizeParameters(params)
+    return {"params": [p.cpu() for p in params], "winner": winner}
+
+
+def verify_sgd_table_empty_partition(results, world, steps0=2) -> None:
+    steps = [0 if r == world - 1 else steps0 + r for r in range(world)]
+    best = max(steps)
+    winner = max(r for r, s in enumerate(steps) if s == best)
+    # the winner's own trajectory: at step s the mean over the ranks still active of 0.1 (s+1) is 0.1 (s+1)
+    want = [torch.full((5,), 2.0 + winner), torch.full((3, 2), -1.0 - winner)]
+    for s in range(best):
+        for w in want:
+            w.sub_(0.1 * (s + 1))
+    for r in range(world):
+        assert results[r]["winner"] == winner
+        for got, w in zip(results[r]["params"], want):
+            torch.testing.assert_close(got, w, rtol=1e-6, atol=1e-6)
+        for a, b in zip(results[r]["params"], results[0]["params"]):
+            assert torch.equal(a, b), "every node must end with the winner's bits"
+
 SCENARIOS = {
     "sgd_reference_test": (run_sgd_reference_test, verify_sgd_reference_test),
     "sgd_fused_uneven": (run_sgd_fused_uneven, verify_sgd_fused_uneven),
@@ -285,4 +322,5 @@ SCENARIOS = {
     "async_ea": (run_async_ea, verify_async_ea),
     "tree_and_metrics": (run_tree_and_metrics, verify_tree_and_metrics),
     "sgd_bucketed": (run_sgd_bucketed, verify_sgd_bucketed),
+    "sgd_table_empty_partition": (run_sgd_table_empty_partition, verify_sgd_table_empty_partition),
 }

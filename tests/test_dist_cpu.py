@@ -54,3 +54,10 @@ def test_tree_facade_and_confusion_matrix():
 def test_bucketed_step_equals_whole_vector_step(world):
     """Per-bucket launches from autograd hooks (uneven steps, drain rounds) give bit-identical parameters."""
     _run("sgd_bucketed", world)
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_table_api_with_an_empty_partition(world):
+    """A node that took no step reaches synchronizeParameters before it ever staged a gradient table: the staging
+    buffers must still sit at the same heap offsets on every node (lua/AllReduceSGD.lua:33-54)."""
+    _run("sgd_table_empty_partition", world)

@@ -169,9 +169,19 @@ class TableStager:
         key = (role, padded, dtype)
         buf = self._cache.get(key)
         if buf is None:
-            buf = self.comm.alloc(padded, dtype, f"stage.{role}")
-            self._cache[key] = buf
+            # Heap offsets must agree across ranks, and ranks do not meet the roles in the same order: a rank whose
+            # partition was empty reaches "params" (synchronizeParameters) before it ever staged a gradient, its peers
+            # the other way round.  So the gradient and parameter staging buffers of one geometry are always carved
+            # out together, in one fixed order, whichever role is asked for first.
+            group = self._PAIRED if role in self._PAIRED else (role,)
+            for r in group:
+                k = (r, padded, dtype)
+                if k not in self._cache:
+                    self._cache[k] = self.comm.alloc(padded, dtype, f"stage.{r}")
+            buf = self._cache[key]
         return buf, padded, tensors
+
+    _PAIRED = ("grads", "params")
 
     @staticmethod
     def pack(buf: SymBuffer, tensors: Sequence[torch.Tensor]) -> None:
