@@ -9,6 +9,7 @@
 //   NVLS     : multimem.ld_reduce + multimem.st (the NVSwitch adds and replicates).
 #include "dl_common.cuh"
 #include "dl_host.h"
+#include "dl_pipe.cuh"
 
 struct ArArgs {
   uint64_t off;
@@ -63,13 +64,12 @@ __global__ void __launch_bounds__(DL_THREADS, 1) allreduce_oneshot_kernel(dl_com
   const int world = c.world;
   const int act = kEmu ? ((a.active >> rank) & 1u) : (a.active & 3u);
   const uint32_t user = kEmu ? a.payload + rank : a.payload;
-  __shared__ unsigned long long auxs[DL_MAX_RANKS];
-  const bool ok = dl_block_barrier(c, rank, world, a.channel, dl_pack_payload(act, user), pay,
-                                   static_cast<unsigned long long>(a.scale != 0), auxs);
+  __shared__ uint32_t auxs[DL_MAX_RANKS];
+  const bool ok = dl_block_barrier<false>(c, rank, world, a.channel, dl_pack_payload(act, user), pay, a.scale != 0 ? 1u : 0u, auxs);
   int n_act;
   const uint32_t mask = dl_active_mask(c, rank, world, a.channel, pay, &n_act);
   // whether to normalise is dictated by the lowest active rank (draining ranks just follow)
-  a.scale = static_cast<int>(dl_aux_of_first_active(mask, auxs, rank) & 1ull);
+  a.scale = static_cast<int>(dl_aux_of_first_active(mask, auxs, rank) & 1u);
   const unsigned long long stride = static_cast<unsigned long long>(gridDim.x) * DL_THREADS;
   const unsigned long long tid0 = static_cast<unsigned long long>(blockIdx.x) * DL_THREADS + threadIdx.x;
 
@@ -161,13 +161,12 @@ __global__ void __launch_bounds__(DL_THREADS, 1) allreduce_twoshot_kernel(dl_com
   const int world = kWorld ? kWorld : c.world;
   const int act = kEmu ? ((a.active >> rank) & 1u) : (a.active & 3u);
   const uint32_t user = kEmu ? a.payload + rank : a.payload;
-  __shared__ unsigned long long auxs[DL_MAX_RANKS];
-  const bool ok = dl_block_barrier(c, rank, world, a.channel, dl_pack_payload(act, user), pay,
-                                   static_cast<unsigned long long>(a.scale != 0), auxs);
+  __shared__ uint32_t auxs[DL_MAX_RANKS];
+  const bool ok = dl_block_barrier<false>(c, rank, world, a.channel, dl_pack_payload(act, user), pay, a.scale != 0 ? 1u : 0u, auxs);
   int n_act;
   const uint32_t mask = dl_active_mask(c, rank, world, a.channel, pay, &n_act);
   // whether to normalise is dictated by the lowest active rank (draining ranks just follow)
-  a.scale = static_cast<int>(dl_aux_of_first_active(mask, auxs, rank) & 1ull);
+  a.scale = static_cast<int>(dl_aux_of_first_active(mask, auxs, rank) & 1u);
   const DlSlice s = dl_slice(a.nvec, rank, world);
   const unsigned long long stride = static_cast<unsigned long long>(gridDim.x) * DL_THREADS;
   const unsigned long long tid0 = static_cast<unsigned long long>(blockIdx.x) * DL_THREADS + threadIdx.x;
@@ -181,6 +180,40 @@ __global__ void __launch_bounds__(DL_THREADS, 1) allreduce_twoshot_kernel(dl_com
     } else {
       allreduce_slice_pass<W, U, false>(c, a, s, world, mask, inv, tid0, stride);
     }
+  }
+  dl_block_barrier(c, rank, world, a.channel, 0u, pay);
+}
+
+// ---- DL_VARIANT_HYBRID (float32): software-pipelined slice pass, switch + P2P in one launch (dl_pipe.cuh) ----
+template <int W>
+struct ArEpi {
+  float inv;
+  __device__ __forceinline__ float4 p2p(const float4 (&v)[W], unsigned long long) {
+    float4 acc = v[0];
+#pragma unroll
+    for (int j = 1; j < W; ++j) acc = acc + v[j];
+    return dl_scale(acc, inv);
+  }
+  __device__ __forceinline__ float4 mc(const float4& sum, unsigned long long) { return dl_scale(sum, inv); }
+};
+
+template <int kWorld, bool kEmu>
+__global__ void __launch_bounds__(DL_PIPE_THREADS, 1) allreduce_pipe_kernel(dl_comm_t c, ArArgs a) {
+  __shared__ uint32_t pay[DL_MAX_RANKS];
+  __shared__ uint32_t auxs[DL_MAX_RANKS];
+  constexpr int W = kWorld ? kWorld : DL_MAX_RANKS;
+  const int rank = kEmu ? static_cast<int>(blockIdx.y) : c.rank;
+  const int world = kWorld ? kWorld : c.world;
+  const int act = kEmu ? ((a.active >> rank) & 1u) : (a.active & 3u);
+  const uint32_t user = kEmu ? a.payload + rank : a.payload;
+  const bool ok = dl_block_barrier<false>(c, rank, world, a.channel, dl_pack_payload(act, user), pay, a.scale != 0 ? 1u : 0u, auxs);
+  int n_act;
+  const uint32_t mask = dl_active_mask(c, rank, world, a.channel, pay, &n_act);
+  a.scale = static_cast<int>(dl_aux_of_first_active(mask, auxs, rank) & 1u);
+  const DlSlice s = dl_slice_even(a.nvec, rank, world);
+  if (ok) {
+    ArEpi<W> epi{(a.scale && n_act > 1) ? 1.f / static_cast<float>(n_act) : 1.f};
+    dl_pipe_pass<W>(c, rank, world, mask, n_act == world, c.nvls_permille, a.off, a.off, 0, s, epi);
   }
   dl_block_barrier(c, rank, world, a.channel, 0u, pay);
 }
@@ -210,6 +243,8 @@ extern "C" int dl_allreduce(const dl_comm_t* c, int dtype, uint64_t off, uint64_
   a.scale = scale_by_inv_active; a.channel = channel;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   int rc = DL_OK;
+  if (variant == DL_VARIANT_LL)
+    return dl_ll_allreduce(c, dtype, off, n * esz, active, payload, scale_by_inv_active, nblocks, channel, st);
   if (variant == DL_VARIANT_ONESHOT) {
     int nb = dl_check_comm(c, channel, dl_pick_blocks(a.nvec, 1, nblocks));
     if (nb < 0) return nb;
@@ -228,9 +263,28 @@ extern "C" int dl_allreduce(const dl_comm_t* c, int dtype, uint64_t off, uint64_
     }
     return rc;
   }
-  DL_REQUIRE(dtype == DL_F32, "dl_allreduce: two-shot / NVLS variants are float32 only");
+  DL_REQUIRE(dtype == DL_F32, "dl_allreduce: two-shot / NVLS / hybrid variants are float32 only");
   int nb = dl_check_comm(c, channel, dl_pick_blocks((a.nvec + c->world - 1) / c->world, 2, nblocks));
   if (nb < 0) return nb;
+  if (variant == DL_VARIANT_HYBRID) {
+    DL_REQUIRE(n % 8 == 0 && off % 32 == 0, "dl_allreduce: the hybrid variant needs n %% 8 == 0 and a 32-byte aligned offset");
+    DL_REQUIRE(c->nvls_permille >= 0 && c->nvls_permille <= 1000, "dl_allreduce: nvls_permille out of range");
+    DL_REQUIRE(c->nvls_permille == 0 || (c->mc && !c->emulate), "dl_allreduce: nvls_permille > 0 needs a multicast mapping");
+    nb = dl_check_comm(c, channel, dl_pick_blocks((a.nvec + c->world - 1) / c->world / 2 + 1, 1, nblocks));
+    if (nb < 0) return nb;
+#define DL_AR_PIPE(WORLD)                                                                                         \
+    rc = c->emulate ? dl_launch(allreduce_pipe_kernel<WORLD, true>, c, nb, DL_PIPE_THREADS, st, *c, a)            \
+                    : dl_launch(allreduce_pipe_kernel<WORLD, false>, c, nb, DL_PIPE_THREADS, st, *c, a)
+    switch (c->world) {
+      case 1: DL_AR_PIPE(1); break;
+      case 2: DL_AR_PIPE(2); break;
+      case 4: DL_AR_PIPE(4); break;
+      case 8: DL_AR_PIPE(8); break;
+      default: DL_AR_PIPE(0); break;
+    }
+#undef DL_AR_PIPE
+    return rc;
+  }
   if (variant == DL_VARIANT_NVLS) {
     DL_REQUIRE(c->mc && !c->emulate, "dl_allreduce: NVLS variant needs a multicast mapping");
     DL_AR_DISPATCH_WORLD(true, false)

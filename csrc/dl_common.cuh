@@ -2,9 +2,10 @@
 //
 // Signalling model (replaces blocking socket recv): every rank owns
 // a signal pad at the start of its symmetric heap.  Block b of rank r and block b
-// of every peer meet at a *block-level* barrier: r stores (epoch<<32 | payload)
-// into slot [epoch&1][b][r] of every peer's pad with st.release.sys and spins on
-// its own slots with ld.acquire.sys.  Epochs are monotonic device-side counters,
+// of every peer meet at a *block-level* barrier: r stores the packet {epoch, payload,
+// epoch, aux} into slot [epoch&1][b][r] of every peer's pad (after a system-scope
+// release fence when the block has data to publish) and polls its own slots, then
+// fences (acquire).  Epochs are monotonic device-side counters,
 // so a launch needs no host-side sequence number and can sit in a CUDA graph.
 // Two parities are enough: a peer cannot reach barrier e+2 before we have
 // signalled e+1, which we only do after we finished reading the e slots.
@@ -18,11 +19,14 @@
 #define DL_DEFAULT_TIMEOUT_NS (20ull * 1000ull * 1000ull * 1000ull)
 
 struct DlPad {
-  unsigned long long flags[2][DL_MAX_BLOCKS][DL_MAX_RANKS];  // [parity][block][source rank]
-  unsigned long long aux[2][DL_MAX_BLOCKS][DL_MAX_RANKS];    // 64 extra bits published with each flag
+  // [parity][block][source rank]: one 16-byte packet {epoch, payload, epoch, aux}.  The epoch rides in both 8-byte
+  // halves (each half is written atomically), so payload and aux need no ordering between them.
+  uint4 slots[2][DL_MAX_BLOCKS][DL_MAX_RANKS];
   unsigned int epoch[DL_MAX_BLOCKS];                         // this rank's barrier count per block
   dl_result_t result;
-  unsigned int reserved[22];
+  unsigned int ll_epoch;                                     // completed DL_VARIANT_LL calls on this channel
+  unsigned int ll_done;                                      // blocks of the running LL call that have finished
+  unsigned int reserved[20];
 };
 static_assert(sizeof(DlPad) % 16 == 0, "pad alignment");
 
@@ -75,6 +79,24 @@ __device__ __forceinline__ unsigned int dl_ld_acquire_gpu_u32(const unsigned int
 __device__ __forceinline__ void dl_st_release_gpu_u32(unsigned int* p, unsigned int v) {
   asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
+__device__ __forceinline__ void dl_st_relaxed_sys(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long dl_ld_relaxed_sys(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void dl_fence_acquire_sys() { asm volatile("fence.acquire.sys;" ::: "memory"); }
+__device__ __forceinline__ void dl_fence_release_sys() { asm volatile("fence.release.sys;" ::: "memory"); }
+__device__ __forceinline__ void dl_fence_sc_sys() { asm volatile("fence.sc.sys;" ::: "memory"); }
+// Sticky error word in pinned host memory (the host polls it without touching the device).
+__device__ __forceinline__ void dl_host_error(const dl_comm_t& c, int channel, int code) {
+  if (c.host_words != nullptr) {
+    dl_host_words_t* h = static_cast<dl_host_words_t*>(c.host_words);
+    if (atomicCAS_system(&h->error, 0u, static_cast<unsigned int>(-code)) == 0u) h->error_channel = static_cast<unsigned int>(channel);
+  }
+}
 __device__ __forceinline__ unsigned long long dl_globaltimer() {
   unsigned long long t;
   asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
@@ -108,6 +130,32 @@ __device__ __forceinline__ void dl_st_u4(uint4* p, const uint4& v) {
                "r"(v.z), "r"(v.w)
                : "memory");
 }
+// 256-bit accesses (sm_100: LDG.E.ENL2.256 / STG.E.ENL2.256): half the memory instructions per byte on the P2P paths.
+struct dl_f8 {
+  float4 lo, hi;
+};
+__device__ __forceinline__ dl_f8 dl_ld_f8(const float4* p) {  // p must be 32-byte aligned
+  dl_f8 v;
+  asm volatile("ld.global.L1::no_allocate.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=f"(v.lo.x), "=f"(v.lo.y), "=f"(v.lo.z), "=f"(v.lo.w), "=f"(v.hi.x), "=f"(v.hi.y), "=f"(v.hi.z), "=f"(v.hi.w)
+               : "l"(p));
+  return v;
+}
+__device__ __forceinline__ void dl_st_f8(float4* p, const dl_f8& v) {
+  asm volatile("st.global.L1::no_allocate.v8.f32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "f"(v.lo.x), "f"(v.lo.y),
+               "f"(v.lo.z), "f"(v.lo.w), "f"(v.hi.x), "f"(v.hi.y), "f"(v.hi.z), "f"(v.hi.w)
+               : "memory");
+}
+// LL packets: 16 bytes = {data0, flag, data1, flag}; each 8-byte half is written and read atomically, so a
+// reader that sees the flag it waits for in both halves has the data (the protocol NCCL calls LL).
+__device__ __forceinline__ void dl_ll_store(uint4* p, uint32_t d0, uint32_t d1, uint32_t flag) {
+  asm volatile("st.volatile.global.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(d0), "r"(flag), "r"(d1), "r"(flag) : "memory");
+}
+__device__ __forceinline__ uint4 dl_ll_load(const uint4* p) {
+  uint4 v;
+  asm volatile("ld.volatile.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+  return v;
+}
 // NVLS: the switch reads the same offset on every GPU bound to the multicast object and
 // returns the sum; multimem.st replicates one store to all of them.
 __device__ __forceinline__ float4 dl_mc_ld_reduce_f4(const float4* p) {
@@ -140,52 +188,70 @@ __device__ __forceinline__ float4 dl_scale(const float4& a, float s) {
 
 // ---- the block-level cross-rank barrier ---------------------------------------------------
 // All threads of the block must call it.  `pay_out` is a shared array of DL_MAX_RANKS words
-// that receives every rank's payload.  Returns false if the bounded spin timed out (the error
-// word of the local pad is then set and callers skip their data phase).
+// that receives every rank's payload (aux_out, if given, every rank's 32-bit aux word).  Returns
+// false if the bounded spin timed out (the error word of the local pad and the host's sticky error
+// word are then set and callers skip their data phase).
+//
+// kPublish = true : release pattern — everything this block wrote so far (P2P stores into peers'
+//                   heaps included) is visible to whoever sees the flag (fence.release.sys = MEMBAR.SYS
+//                   waits for those writes to be acknowledged, which costs an NVLink round trip).
+// kPublish = false: arrival only — "my inputs are final and your stores may land in my outputs".  The inputs
+//                   were written by earlier kernels on this stream, so they already sit at this GPU's point
+//                   of coherence, where peer loads and the switch are served; no fence, one NVLink crossing.
+// Both sides poll with relaxed loads and fence once (acquire) after the last flag arrived.
+template <bool kPublish = true>
 __device__ __forceinline__ bool dl_block_barrier(const dl_comm_t& c, int rank, int world, int ch,
                                                  uint32_t payload, uint32_t* pay_out,
-                                                 unsigned long long aux = 0ull,
-                                                 unsigned long long* aux_out = nullptr) {
+                                                 uint32_t aux = 0u, uint32_t* aux_out = nullptr) {
   __shared__ int s_ok;
-  __syncthreads();  // everything this block wrote so far is ordered before the release below
+  __syncthreads();  // everything this block wrote so far is ordered before the fence below
   if (threadIdx.x < 32) {
     DlPad* mine = dl_pad(c, rank, ch);
     const int lane = threadIdx.x;
     uint32_t e = 0;
     if (lane == 0) e = mine->epoch[blockIdx.x] + 1u;
     e = __shfl_sync(0xffffffffu, e, 0);
-    bool ok = true;
+    int err = 0;
     if (lane < world) {
       DlPad* theirs = dl_pad(c, lane, ch);
-      if (aux_out != nullptr)  // ordered before the flag by the release below
-        *reinterpret_cast<volatile unsigned long long*>(&theirs->aux[e & 1u][blockIdx.x][rank]) = aux;
-      dl_st_release_sys(&theirs->flags[e & 1u][blockIdx.x][rank],
-                        (static_cast<unsigned long long>(e) << 32) | payload);
-      const unsigned long long* slot = &mine->flags[e & 1u][blockIdx.x][lane];
+      if (kPublish) dl_fence_release_sys();
+      // packet {epoch, payload, epoch, aux} in one 16-byte store
+      asm volatile("st.volatile.global.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(&theirs->slots[e & 1u][blockIdx.x][rank]),
+                   "r"(e), "r"(payload), "r"(e), "r"(aux)
+                   : "memory");
+      const uint4* slot = &mine->slots[e & 1u][blockIdx.x][lane];
       const unsigned long long limit = c.timeout_ns ? c.timeout_ns : DL_DEFAULT_TIMEOUT_NS;
       unsigned long long t0 = 0;
       unsigned int polls = 0;
-      unsigned long long w;
+      uint4 w;
       while (true) {
-        w = dl_ld_acquire_sys(slot);
-        if (static_cast<uint32_t>(w >> 32) == e) break;
+        w = dl_ll_load(slot);
+        if (w.x == e && w.z == e) break;
+        if (c.flags & DL_FLAG_DEBUG) {
+          // a slot of parity e&1 can only hold e-2 (its previous use; 0 before the first) or e: anything else
+          // means a rank ran ahead, a launch went missing, or somebody else wrote into the pad
+          const uint32_t prev = e - 2u;
+          const bool okx = w.x == e || w.x == prev || (e <= 2u && w.x == 0u);
+          const bool okz = w.z == e || w.z == prev || (e <= 2u && w.z == 0u);
+          if (!okx || !okz) { err = DL_EPROTO; break; }
+        }
         if ((++polls & 1023u) == 0u) {
           const unsigned long long now = dl_globaltimer();
           if (t0 == 0) t0 = now;
-          if (now - t0 > limit) {
-            ok = false;
-            break;
-          }
+          if (now - t0 > limit) { err = DL_ETIMEOUT; break; }
         }
       }
-      pay_out[lane] = static_cast<uint32_t>(w);
-      if (aux_out != nullptr)
-        aux_out[lane] = *reinterpret_cast<volatile unsigned long long*>(&mine->aux[e & 1u][blockIdx.x][lane]);
+      dl_fence_acquire_sys();
+      pay_out[lane] = w.y;
+      if (aux_out != nullptr) aux_out[lane] = w.w;
     }
-    ok = __all_sync(0xffffffffu, ok);
+    const bool ok = __all_sync(0xffffffffu, err == 0);
+    if (err != 0) {
+      mine->result.error = static_cast<uint32_t>(-err);
+      dl_host_error(c, ch, err);
+    }
     if (lane == 0) {
       mine->epoch[blockIdx.x] = e;
-      if (!ok) mine->result.error = static_cast<uint32_t>(-DL_ETIMEOUT);
       s_ok = ok ? 1 : 0;
     }
   }
@@ -215,13 +281,21 @@ __device__ __forceinline__ uint32_t dl_active_mask(const dl_comm_t& c, int rank,
     DlPad* mine = dl_pad(c, rank, ch);
     for (int j = 0; j < DL_MAX_RANKS; ++j) mine->result.payload[j] = j < world ? (pay[j] >> 2) : 0u;
     mine->result.n_active = static_cast<uint32_t>(n);
+    if (c.host_words != nullptr && rank == c.rank) {
+      // the contributor count, readable by the host without a device-to-host copy (lua/AllReduceSGD.lua:20: `_, n = allReduce`)
+      dl_host_words_t* h = static_cast<dl_host_words_t*>(c.host_words);
+      volatile uint32_t* slot = &h->ring[ch][c.ticket % DL_HOST_RING].ticket;
+      slot[1] = static_cast<uint32_t>(n);
+      __threadfence_system();
+      slot[0] = c.ticket;
+    }
   }
   return mask;
 }
 
 // Hyper-parameters travel in the aux word so that ACTIVE ranks dictate them: a draining rank
 // (lua/AllReduceSGD.lua:37) only needs to know the buffer geometry, not the current lr.
-__device__ __forceinline__ unsigned long long dl_aux_of_first_active(uint32_t mask, const unsigned long long* aux, int rank) {
+__device__ __forceinline__ uint32_t dl_aux_of_first_active(uint32_t mask, const uint32_t* aux, int rank) {
   const int first = mask ? (__ffs(static_cast<int>(mask)) - 1) : rank;
   return aux[first];
 }

@@ -108,6 +108,14 @@ extern "C" int dl_read_result(const dl_comm_t* c, int channel, dl_result_t* out,
   DL_CUDA(cudaMemcpyAsync(out, &pad->result, sizeof(dl_result_t), cudaMemcpyDeviceToHost, st));
   DL_CUDA(cudaStreamSynchronize(st));
   if (out->error) {
+    // reported once: clear the device word so that later calls are judged on their own
+    DL_CUDA(cudaMemsetAsync(const_cast<uint32_t*>(&pad->result.error), 0, sizeof(uint32_t), st));
+    DL_CUDA(cudaStreamSynchronize(st));
+    if (static_cast<int>(out->error) == -DL_EPROTO) {
+      dl_set_error("collective on channel %d found a barrier slot the protocol cannot produce (rank %d of %d): ranks are not "
+                   "launching the same sequence of collectives, or something else wrote into the signal pad", channel, c->rank, c->world);
+      return DL_EPROTO;
+    }
     dl_set_error("collective on channel %d timed out waiting for a peer (rank %d of %d)", channel, c->rank, c->world);
     return DL_ETIMEOUT;
   }
@@ -123,6 +131,24 @@ extern "C" int dl_reset_pad(const dl_comm_t* c) {
     DL_CUDA(cudaMemset(c->base[c->rank], 0, DL_PAD_BYTES));
   }
   DL_CUDA(cudaDeviceSynchronize());
+  return DL_OK;
+}
+
+// Pinned, device-mapped host memory for dl_comm_t.host_words: kernels write the contributor count and the sticky
+// error word there, the host reads them with plain loads (no copy, no stream synchronisation of its own).
+extern "C" int dl_host_words_alloc(void** host_ptr, void** dev_ptr) {
+  DL_REQUIRE(host_ptr && dev_ptr, "dl_host_words_alloc: null pointer");
+  void* h = nullptr;
+  DL_CUDA(cudaHostAlloc(&h, sizeof(dl_host_words_t), cudaHostAllocMapped | cudaHostAllocPortable));
+  memset(h, 0, sizeof(dl_host_words_t));
+  void* d = nullptr;
+  DL_CUDA(cudaHostGetDevicePointer(&d, h, 0));
+  *host_ptr = h;
+  *dev_ptr = d;
+  return DL_OK;
+}
+extern "C" int dl_host_words_free(void* host_ptr) {
+  if (host_ptr) DL_CUDA(cudaFreeHost(host_ptr));
   return DL_OK;
 }
 

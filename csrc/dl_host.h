@@ -34,6 +34,16 @@ int dl_sm_count();
 // Default block count for `work_items` items of per-thread work.
 int dl_pick_blocks(unsigned long long work_items, int per_thread, int requested);
 
+// DL_VARIANT_LL forms of the collectives (csrc/ll_ops.cu); reached through the public entry points.
+int dl_ll_allreduce(const dl_comm_t* c, int dtype, uint64_t off, uint64_t nbytes, int active, uint32_t payload, int scale,
+                    int nblocks, int channel, cudaStream_t st);
+int dl_ll_sgd(const dl_comm_t* c, uint64_t g_off, uint64_t p_off, uint64_t m_off, uint64_t n, float lr, float momentum, float wd,
+              int nesterov, int active, uint32_t payload, int zero_grads, int nblocks, int channel, cudaStream_t st);
+int dl_ll_ea(const dl_comm_t* c, uint64_t x_off, uint64_t c_off, uint64_t cnew_off, uint64_t n, float alpha, int active,
+             uint32_t payload, int nblocks, int channel, cudaStream_t st);
+int dl_ll_broadcast(const dl_comm_t* c, uint64_t off, uint64_t off2, uint64_t n, int root, uint32_t payload, int nblocks, int channel,
+                    cudaStream_t st);
+
 // Launch `kernel` normally, or cooperatively with gridDim.y = world when emulating ranks.
 template <typename... Args>
 int dl_launch(void (*kernel)(Args...), const dl_comm_t* c, int nblocks, int threads,

@@ -17,6 +17,7 @@
 // A round in which no rank is active (the terminating drain round) moves nothing.
 #include "dl_common.cuh"
 #include "dl_host.h"
+#include "dl_pipe.cuh"
 
 struct EaArgs {
   uint64_t x_off, c_off, cnew_off;
@@ -35,7 +36,7 @@ __global__ void __launch_bounds__(DL_THREADS, 1) fused_ea_kernel(dl_comm_t c, Ea
   const int world = kWorld ? kWorld : c.world;
   const int act = kEmu ? ((a.active >> rank) & 1u) : (a.active & 3u);
   const uint32_t user = kEmu ? a.payload + rank : a.payload;
-  const bool ok = dl_block_barrier(c, rank, world, a.channel, dl_pack_payload(act, user), pay);
+  const bool ok = dl_block_barrier<false>(c, rank, world, a.channel, dl_pack_payload(act, user), pay);
   int n_act;
   dl_active_mask(c, rank, world, a.channel, pay, &n_act);
   const DlSlice s = dl_slice(a.n4, rank, world);
@@ -127,6 +128,71 @@ __global__ void __launch_bounds__(DL_THREADS, 1) fused_ea_kernel(dl_comm_t c, Ea
   }
 }
 
+// ---- DL_VARIANT_HYBRID: software-pipelined slice pass, switch + P2P in one launch (dl_pipe.cuh) ------------
+template <int W>
+struct EaEpi {
+  const float4* c_old;
+  float alpha;
+  int world;
+  __device__ __forceinline__ float4 p2p(const float4 (&v)[W], unsigned long long idx) {
+    const float4 cc = c_old[idx];
+    float4 sum = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+    for (int j = 0; j < W; ++j) {
+      if (j < world) {  // same expression as the reference: delta_j = (x_j - c) * alpha, summed in rank order
+        sum.x += (v[j].x - cc.x) * alpha; sum.y += (v[j].y - cc.y) * alpha;
+        sum.z += (v[j].z - cc.z) * alpha; sum.w += (v[j].w - cc.w) * alpha;
+      }
+    }
+    return cc + sum;
+  }
+  __device__ __forceinline__ float4 mc(const float4& sx, unsigned long long idx) {
+    // switch-side sum of x over all ranks: sum_j a(x_j - c) = a (sum_j x_j - N c)
+    const float4 cc = c_old[idx];
+    const float nw = static_cast<float>(world);
+    return cc + make_float4(alpha * (sx.x - nw * cc.x), alpha * (sx.y - nw * cc.y), alpha * (sx.z - nw * cc.z), alpha * (sx.w - nw * cc.w));
+  }
+};
+
+template <int kWorld, bool kEmu>
+__global__ void __launch_bounds__(DL_PIPE_THREADS, 1) fused_ea_pipe_kernel(dl_comm_t c, EaArgs a) {
+  __shared__ uint32_t pay[DL_MAX_RANKS];
+  constexpr int W = kWorld ? kWorld : DL_MAX_RANKS;
+  const int rank = kEmu ? static_cast<int>(blockIdx.y) : c.rank;
+  const int world = kWorld ? kWorld : c.world;
+  const int act = kEmu ? ((a.active >> rank) & 1u) : (a.active & 3u);
+  const uint32_t user = kEmu ? a.payload + rank : a.payload;
+  const bool ok = dl_block_barrier<false>(c, rank, world, a.channel, dl_pack_payload(act, user), pay);
+  int n_act;
+  dl_active_mask(c, rank, world, a.channel, pay, &n_act);
+  const DlSlice s = dl_slice_even(a.n4, rank, world);
+  const bool go = ok && n_act > 0;
+  const float4* c_old = dl_at<float4>(c, rank, a.c_off);
+  const float alpha = a.alpha;
+  if (go) {
+    // every rank's x takes part whoever is "active" (a finished node still moves, lua/AllReduceEA.lua:58-68),
+    // so the switch may always add all copies
+    EaEpi<W> epi{c_old, alpha, world};
+    dl_pipe_pass<W>(c, rank, world, (1u << world) - 1u, true, c.nvls_permille, a.x_off, a.cnew_off, 0, s, epi);
+  }
+  const bool ok2 = dl_block_barrier(c, rank, world, a.channel, 0u, pay);
+  if (go && ok2) {
+    float4* x = dl_at<float4>(c, rank, a.x_off);
+    dl_pipe_foreach_released(a.n4, world, true, c.mc != nullptr, c.nvls_permille, s, [&](unsigned long long k) {
+      float4 xv = x[k];
+      const float4 cv = c_old[k];
+      xv.x -= (xv.x - cv.x) * alpha; xv.y -= (xv.y - cv.y) * alpha;
+      xv.z -= (xv.z - cv.z) * alpha; xv.w -= (xv.w - cv.w) * alpha;
+      x[k] = xv;
+    });
+  } else if (ok && ok2) {
+    float4* cn = dl_at<float4>(c, rank, a.cnew_off);
+    const unsigned long long stride = static_cast<unsigned long long>(gridDim.x) * DL_PIPE_THREADS;
+    for (unsigned long long k = static_cast<unsigned long long>(blockIdx.x) * DL_PIPE_THREADS + threadIdx.x; k < a.n4; k += stride)
+      cn[k] = c_old[k];
+  }
+}
+
 // single-rank elastic step (world == 1 / oracle for tests):  d = a(x-c); x -= d; c += d
 __global__ void __launch_bounds__(DL_THREADS) local_ea_kernel(float* x, float* c, unsigned long long n, float alpha) {
   const unsigned long long stride = static_cast<unsigned long long>(gridDim.x) * DL_THREADS;
@@ -158,10 +224,32 @@ extern "C" int dl_fused_ea(const dl_comm_t* c, uint64_t x_off, uint64_t c_off, u
   EaArgs a;
   a.x_off = x_off; a.c_off = c_off; a.cnew_off = cnew_off; a.n4 = n / 4; a.alpha = alpha;
   a.active = static_cast<uint32_t>(active); a.payload = payload; a.channel = channel;
+  if (variant == DL_VARIANT_LL)
+    return dl_ll_ea(c, x_off, c_off, cnew_off, n, alpha, active, payload, nblocks, channel, static_cast<cudaStream_t>(stream));
   int nb = dl_check_comm(c, channel, dl_pick_blocks((a.n4 + c->world - 1) / (c->world > 0 ? c->world : 1), 2, nblocks));
   if (nb < 0) return nb;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   int rc = DL_OK;
+  if (variant == DL_VARIANT_HYBRID) {
+    DL_REQUIRE(n % 8 == 0 && x_off % 32 == 0 && c_off % 32 == 0 && cnew_off % 32 == 0,
+               "dl_fused_ea: the hybrid variant needs n %% 8 == 0 and 32-byte aligned offsets");
+    DL_REQUIRE(c->nvls_permille >= 0 && c->nvls_permille <= 1000, "dl_fused_ea: nvls_permille out of range");
+    DL_REQUIRE(c->nvls_permille == 0 || (c->mc && !c->emulate), "dl_fused_ea: nvls_permille > 0 needs a multicast mapping");
+    nb = dl_check_comm(c, channel, dl_pick_blocks((a.n4 + c->world - 1) / (c->world > 0 ? c->world : 1) / 2 + 1, 1, nblocks));
+    if (nb < 0) return nb;
+#define DL_EA_PIPE(WORLD)                                                                                        \
+    rc = c->emulate ? dl_launch(fused_ea_pipe_kernel<WORLD, true>, c, nb, DL_PIPE_THREADS, st, *c, a)            \
+                    : dl_launch(fused_ea_pipe_kernel<WORLD, false>, c, nb, DL_PIPE_THREADS, st, *c, a)
+    switch (c->world) {
+      case 1: DL_EA_PIPE(1); break;
+      case 2: DL_EA_PIPE(2); break;
+      case 4: DL_EA_PIPE(4); break;
+      case 8: DL_EA_PIPE(8); break;
+      default: DL_EA_PIPE(0); break;
+    }
+#undef DL_EA_PIPE
+    return rc;
+  }
   if (variant == DL_VARIANT_NVLS) {
     DL_REQUIRE(c->mc && !c->emulate, "dl_fused_ea: NVLS variant needs a multicast mapping");
     DL_EA_DISPATCH_WORLD(true, false)

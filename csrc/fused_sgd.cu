@@ -16,6 +16,7 @@
 // Parameters stay bit-identical on all ranks because only the owner computes a slice.
 #include "dl_common.cuh"
 #include "dl_host.h"
+#include "dl_pipe.cuh"
 
 struct SgdArgs {
   uint64_t g_off, p_off, m_off;
@@ -122,13 +123,12 @@ __global__ void __launch_bounds__(DL_THREADS, 1) sgd_twoshot_kernel(dl_comm_t c,
   const int act = kEmu ? ((a.active >> rank) & 1u) : (a.active & 3u);
   const uint32_t user = kEmu ? a.payload + rank : a.payload;
 
-  __shared__ unsigned long long auxs[DL_MAX_RANKS];
-  const bool ok = dl_block_barrier(c, rank, world, a.channel, dl_pack_payload(act, user), pay,
-                                   static_cast<unsigned long long>(__float_as_uint(a.lr)), auxs);
+  __shared__ uint32_t auxs[DL_MAX_RANKS];
+  const bool ok = dl_block_barrier<false>(c, rank, world, a.channel, dl_pack_payload(act, user), pay, __float_as_uint(a.lr), auxs);
   int n_act;
   const uint32_t mask = dl_active_mask(c, rank, world, a.channel, pay, &n_act);
   // the learning rate of the lowest active rank wins (identical on all ranks, so owners agree)
-  a.lr = __uint_as_float(static_cast<uint32_t>(dl_aux_of_first_active(mask, auxs, rank)));
+  a.lr = __uint_as_float(dl_aux_of_first_active(mask, auxs, rank));
   const DlSlice s = dl_slice(a.n4, rank, world);
   const unsigned long long stride = static_cast<unsigned long long>(gridDim.x) * DL_THREADS;
   const unsigned long long tid0 = static_cast<unsigned long long>(blockIdx.x) * DL_THREADS + threadIdx.x;
@@ -160,6 +160,54 @@ __global__ void __launch_bounds__(DL_THREADS, 1) sgd_twoshot_kernel(dl_comm_t c,
   }
 }
 
+// ---- DL_VARIANT_HYBRID: software-pipelined slice pass, switch + P2P in one launch (dl_pipe.cuh) --------
+template <int W>
+struct SgdEpi {
+  const SgdArgs& a;
+  float4* p_loc;
+  float4* m_loc;
+  float inv;
+  __device__ __forceinline__ float4 upd(const float4& sum, unsigned long long idx) {
+    return sgd_update(dl_scale(sum, inv), p_loc[idx], m_loc ? m_loc + idx : nullptr, a);
+  }
+  __device__ __forceinline__ float4 p2p(const float4 (&v)[W], unsigned long long idx) {
+    float4 acc = v[0];
+#pragma unroll
+    for (int j = 1; j < W; ++j) acc = acc + v[j];  // rank order, zeros for ranks that sit this round out
+    return upd(acc, idx);
+  }
+  __device__ __forceinline__ float4 mc(const float4& sum, unsigned long long idx) { return upd(sum, idx); }
+};
+
+template <int kWorld, bool kEmu>
+__global__ void __launch_bounds__(DL_PIPE_THREADS, 1) sgd_pipe_kernel(dl_comm_t c, SgdArgs a) {
+  __shared__ uint32_t pay[DL_MAX_RANKS];
+  __shared__ uint32_t auxs[DL_MAX_RANKS];
+  constexpr int W = kWorld ? kWorld : DL_MAX_RANKS;
+  const int rank = kEmu ? static_cast<int>(blockIdx.y) : c.rank;
+  const int world = kWorld ? kWorld : c.world;
+  const int act = kEmu ? ((a.active >> rank) & 1u) : (a.active & 3u);
+  const uint32_t user = kEmu ? a.payload + rank : a.payload;
+  const bool ok = dl_block_barrier<false>(c, rank, world, a.channel, dl_pack_payload(act, user), pay, __float_as_uint(a.lr), auxs);
+  int n_act;
+  const uint32_t mask = dl_active_mask(c, rank, world, a.channel, pay, &n_act);
+  a.lr = __uint_as_float(dl_aux_of_first_active(mask, auxs, rank));
+  const DlSlice s = dl_slice_even(a.n4, rank, world);
+  const bool full = n_act == world;
+  if (ok && n_act > 0) {
+    SgdEpi<W> epi{a, dl_at<float4>(c, rank, a.p_off), a.m_off ? dl_at<float4>(c, rank, a.m_off) : nullptr,
+                  n_act > 1 ? 1.f / static_cast<float>(n_act) : 1.f};
+    dl_pipe_pass<W>(c, rank, world, mask, full, c.nvls_permille, a.g_off, a.p_off, 0, s, epi);
+  }
+  const bool ok2 = dl_block_barrier(c, rank, world, a.channel, 0u, pay);
+  if (ok && ok2 && a.zero_grads) {
+    float4* g_loc = dl_at<float4>(c, rank, a.g_off);
+    const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+    // a round nobody contributed to ran no data phase: its geometry is the all-P2P one
+    dl_pipe_foreach_released(a.n4, world, full, c.mc != nullptr, c.nvls_permille, s, [&](unsigned long long k) { g_loc[k] = z; });
+  }
+}
+
 template <int kWorld, bool kEmu>
 __global__ void __launch_bounds__(DL_THREADS, 1) sgd_oneshot_kernel(dl_comm_t c, SgdArgs a) {
   __shared__ uint32_t pay[DL_MAX_RANKS];
@@ -170,13 +218,12 @@ __global__ void __launch_bounds__(DL_THREADS, 1) sgd_oneshot_kernel(dl_comm_t c,
   const int act = kEmu ? ((a.active >> rank) & 1u) : (a.active & 3u);
   const uint32_t user = kEmu ? a.payload + rank : a.payload;
 
-  __shared__ unsigned long long auxs[DL_MAX_RANKS];
-  const bool ok = dl_block_barrier(c, rank, world, a.channel, dl_pack_payload(act, user), pay,
-                                   static_cast<unsigned long long>(__float_as_uint(a.lr)), auxs);
+  __shared__ uint32_t auxs[DL_MAX_RANKS];
+  const bool ok = dl_block_barrier<false>(c, rank, world, a.channel, dl_pack_payload(act, user), pay, __float_as_uint(a.lr), auxs);
   int n_act;
   const uint32_t mask = dl_active_mask(c, rank, world, a.channel, pay, &n_act);
   // the learning rate of the lowest active rank wins (identical on all ranks, so owners agree)
-  a.lr = __uint_as_float(static_cast<uint32_t>(dl_aux_of_first_active(mask, auxs, rank)));
+  a.lr = __uint_as_float(dl_aux_of_first_active(mask, auxs, rank));
   const unsigned long long stride = static_cast<unsigned long long>(gridDim.x) * DL_THREADS;
   const unsigned long long tid0 = static_cast<unsigned long long>(blockIdx.x) * DL_THREADS + threadIdx.x;
 
@@ -268,11 +315,35 @@ extern "C" int dl_fused_sgd(const dl_comm_t* c, uint64_t g_off, uint64_t p_off, 
   a.g_off = g_off; a.p_off = p_off; a.m_off = m_off; a.n4 = n / 4;
   a.lr = lr; a.momentum = momentum; a.wd = weight_decay; a.nesterov = nesterov;
   a.active = static_cast<uint32_t>(active); a.payload = payload; a.zero_grads = zero_grads; a.channel = channel;
+  if (variant == DL_VARIANT_LL)
+    return dl_ll_sgd(c, g_off, p_off, m_off, n, lr, momentum, weight_decay, nesterov, active, payload, zero_grads, nblocks, channel,
+                     static_cast<cudaStream_t>(stream));
   const unsigned long long work = variant == DL_VARIANT_ONESHOT ? a.n4 : (a.n4 + c->world - 1) / (c->world > 0 ? c->world : 1);
   int nb = dl_check_comm(c, channel, dl_pick_blocks(work, 2, nblocks));
   if (nb < 0) return nb;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   int rc = DL_OK;
+  if (variant == DL_VARIANT_HYBRID) {
+    DL_REQUIRE(n % 8 == 0 && g_off % 32 == 0 && p_off % 32 == 0 && m_off % 32 == 0,
+               "dl_fused_sgd: the hybrid variant moves 32 bytes at a time: n %% 8 == 0 and 32-byte aligned offsets");
+    DL_REQUIRE(c->nvls_permille >= 0 && c->nvls_permille <= 1000, "dl_fused_sgd: nvls_permille out of range");
+    DL_REQUIRE(c->nvls_permille == 0 || (c->mc && !c->emulate), "dl_fused_sgd: nvls_permille > 0 needs a multicast mapping");
+    // 256 threads per CTA, one 32-byte item per thread and stage: enough CTAs for ~2 items per thread, all SMs at most
+    nb = dl_check_comm(c, channel, dl_pick_blocks(work / 2 + 1, 2 * DL_PIPE_THREADS / DL_THREADS, nblocks));
+    if (nb < 0) return nb;
+#define DL_SGD_PIPE(WORLD)                                                                                      \
+    rc = c->emulate ? dl_launch(sgd_pipe_kernel<WORLD, true>, c, nb, DL_PIPE_THREADS, st, *c, a)                  \
+                    : dl_launch(sgd_pipe_kernel<WORLD, false>, c, nb, DL_PIPE_THREADS, st, *c, a)
+    switch (c->world) {
+      case 1: DL_SGD_PIPE(1); break;
+      case 2: DL_SGD_PIPE(2); break;
+      case 4: DL_SGD_PIPE(4); break;
+      case 8: DL_SGD_PIPE(8); break;
+      default: DL_SGD_PIPE(0); break;
+    }
+#undef DL_SGD_PIPE
+    return rc;
+  }
   if (variant == DL_VARIANT_ONESHOT) {
     if (c->emulate) { DL_SGD_DISPATCH_WORLD(sgd_oneshot_kernel, true) } else { DL_SGD_DISPATCH_WORLD(sgd_oneshot_kernel, false) }
   } else if (variant == DL_VARIANT_NVLS) {

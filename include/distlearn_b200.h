@@ -29,10 +29,20 @@ extern "C" {
 #define DL_ESYS (-4)
 #define DL_ETIMEOUT (-5)
 
+#define DL_EPROTO (-6) /* DL_FLAG_DEBUG: a barrier slot held an epoch the protocol cannot produce */
+
 /* collective algorithm variants (chosen per message size by the variant table) */
 #define DL_VARIANT_ONESHOT 0 /* every rank reads all peers, reduces in rank order          */
 #define DL_VARIANT_TWOSHOT 1 /* owner-computes reduce-scatter + push all-gather over P2P   */
 #define DL_VARIANT_NVLS 2    /* multimem.ld_reduce + multimem.st through the NVSwitch      */
+#define DL_VARIANT_LL 3      /* small messages: every rank pushes {data, flag} packets into its peers' staging
+                                slots and reduces what arrives - one NVLink crossing, no barrier at all */
+#define DL_VARIANT_HYBRID 4  /* large messages: software-pipelined slice pass, part of every slice reduced in the
+                                switch (multimem) and the rest over P2P loads in the same launch; nvls_permille
+                                in dl_comm_t sets the split (0 = all P2P, 1000 = all NVLS) */
+
+/* dl_comm_t.flags */
+#define DL_FLAG_DEBUG 1u     /* barriers check epoch monotonicity / slot contents and report DL_EPROTO */
 
 /* data types of the plain all-reduce */
 #define DL_F32 0
@@ -52,11 +62,30 @@ typedef struct dl_comm {
   int32_t rank;
   int32_t world;
   int32_t emulate;
-  int32_t reserved;
+  uint32_t flags;      /* DL_FLAG_* */
   void* base[DL_MAX_RANKS];
   void* mc;
   uint64_t timeout_ns; /* bounded spin: 0 = default 20 s */
+  /* Small-message (DL_VARIANT_LL) staging area inside every heap: DL_NUM_CHANNELS x 2 parities x world source
+   * slots of ll_slot_bytes each, starting at heap offset ll_off (0 = not set up).  A slot holds one 16-byte
+   * header packet plus two 16-byte packets per 16 bytes of payload; it must start out zeroed. */
+  uint64_t ll_off;
+  uint64_t ll_slot_bytes;
+  /* Device-visible address of pinned host memory (dl_host_words_t) or NULL: kernels leave n_active there under the
+   * caller's ticket, and the sticky error word, so the host can read both without a device-to-host copy. */
+  void* host_words;
+  uint32_t ticket;       /* caller's sequence number for this call (host_words ring index) */
+  int32_t nvls_permille; /* DL_VARIANT_HYBRID: share of every slice that goes through the switch */
 } dl_comm_t;
+
+/* What kernels write into pinned host memory (one per communicator). */
+#define DL_HOST_RING 64
+typedef struct dl_host_words {
+  uint32_t error;                            /* sticky: 0, or the positive DL_E* code of the first failure */
+  uint32_t error_channel;
+  uint32_t reserved[2];
+  struct { uint32_t ticket, n_active; } ring[DL_NUM_CHANNELS][DL_HOST_RING];
+} dl_host_words_t;
 
 /* Per-call result words the kernels leave in the local signal pad. */
 typedef struct dl_result {
@@ -131,6 +160,24 @@ int dl_fused_ea(const dl_comm_t* c, uint64_t x_off, uint64_t c_off, uint64_t cne
  * lua/AllReduceEA.lua:93-99). */
 int dl_broadcast(const dl_comm_t* c, uint64_t off, uint64_t off2, uint64_t n, int root, int variant,
                  uint32_t payload, int nblocks, int channel, void* stream);
+
+/* Pinned, device-mapped host memory for dl_comm_t.host_words (one dl_host_words_t, zeroed).  With it set, every
+ * collective leaves its contributor count under dl_comm_t.ticket in ring[channel][ticket % DL_HOST_RING] and a
+ * failed spin sets the sticky `error` word, both readable by the host with plain loads: the `n` that
+ * lua/AllReduceSGD.lua:20-29 returns costs no device-to-host copy. */
+int dl_host_words_alloc(void** host_ptr, void** dev_ptr);
+int dl_host_words_free(void* host_ptr);
+
+/* Memory-model litmus tests of the signalling patterns on the real fabric (csrc/litmus.cu; the reference has no
+ * counterpart - it synchronises with blocking sockets).  shape 0 = message passing around the ring of ranks (data
+ * stores, release fence, flag | poll, acquire fence, data loads), shape 1 = store buffering with fence.sc.sys;
+ * fenced = 0 drops the fences (control run).  Block b of a rank plays against block b of its neighbours with a random
+ * __nanosleep skew per iteration.  scratch: dl_litmus_scratch_bytes(iterations, nblocks) zeroed bytes at scratch_off on
+ * every rank; afterwards its first words hold {checked, violations (MP), blocks that timed out} as u64, and for SB the
+ * per-iteration loaded values follow per block (see csrc/litmus.cu). */
+size_t dl_litmus_scratch_bytes(int iterations, int nblocks);
+int dl_litmus(const dl_comm_t* c, int shape, int fenced, uint64_t scratch_off, int iterations, uint32_t seed, int nblocks,
+              void* stream);
 
 /* A barrier only: publishes payload/active, fills dl_result. */
 int dl_barrier(const dl_comm_t* c, int active, uint32_t payload, int channel, void* stream);

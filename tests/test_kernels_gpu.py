@@ -34,12 +34,15 @@ def test_library_is_native_and_loaded():
 
 
 @pytest.mark.parametrize("world", [2, 4, 8, 3])
-@pytest.mark.parametrize("variant", ["oneshot", "twoshot"])
+@pytest.mark.parametrize("variant", ["oneshot", "twoshot", "hybrid", "ll"])
 @pytest.mark.parametrize("n", [64, 4096 + 32, 300000])
 def test_allreduce_f32(world, variant, n):
     if variant == "oneshot":
         n = min(n, 100000)   # one-shot keeps the whole vector in registers: capacity-bound by design
     comm = _emu(world)
+    if variant == "ll":
+        assert comm.ll_max_bytes >= 4096
+        n = min(n, comm.ll_max_bytes // 4)   # the push path is for small messages: capped by its staging area
     buf, views = comm.alloc_all(n)
     vals = [_rand(n, 10 + r) for r in range(world)]
     for v, t in zip(views, vals):
@@ -54,15 +57,16 @@ def test_allreduce_f32(world, variant, n):
     assert res.n_active == world and res.payloads == [5 + r for r in range(world)]
 
 
+@pytest.mark.parametrize("variant", ["oneshot", "ll"])
 @pytest.mark.parametrize("dtype", [torch.int64, torch.int32, torch.float64])
-def test_allreduce_other_dtypes(dtype):
+def test_allreduce_other_dtypes(dtype, variant):
     world, n = 4, 100 if dtype != torch.int32 else 200
     comm = _emu(world)
     buf, views = comm.alloc_all(n, dtype)
     vals = [_rand(n, 20 + r, dtype) for r in range(world)]
     for v, t in zip(views, vals):
         v.copy_(t)
-    comm.allreduce(buf, n, active=0b1111, variant="oneshot", nblocks=2)
+    comm.allreduce(buf, n, active=0b1111, variant=variant, nblocks=2)
     torch.cuda.synchronize()
     want, _ = oracle.allreduce_sum(vals)
     for v in views:
@@ -72,7 +76,7 @@ def test_allreduce_other_dtypes(dtype):
             assert torch.equal(v.cpu(), want)
 
 
-@pytest.mark.parametrize("variant", ["oneshot", "twoshot"])
+@pytest.mark.parametrize("variant", ["oneshot", "twoshot", "hybrid", "ll"])
 def test_allreduce_inactive_and_normalise(variant):
     world, n = 4, 2048
     comm = _emu(world)
@@ -89,11 +93,15 @@ def test_allreduce_inactive_and_normalise(variant):
 
 
 @pytest.mark.parametrize("world", [1, 2, 4, 8, 5])
-@pytest.mark.parametrize("variant", ["oneshot", "twoshot"])
+@pytest.mark.parametrize("variant", ["oneshot", "twoshot", "hybrid", "ll"])
 @pytest.mark.parametrize("momentum,wd,nesterov", [(0.0, 0.0, False), (0.9, 1e-3, False), (0.9, 0.0, True)])
 def test_fused_sgd(world, variant, momentum, wd, nesterov):
     n, lr = 50016, 0.05
     comm = _emu(world)
+    if variant == "ll":
+        if world == 1:
+            pytest.skip("a single rank has nobody to push to")
+        n = comm.ll_max_bytes // 4
     g_buf, g_views = comm.alloc_all(n)
     p_buf, p_views = comm.alloc_all(n)
     m_buf, m_views = comm.alloc_all(n) if momentum else (None, None)
@@ -134,9 +142,14 @@ def test_fused_sgd_lr_comes_from_the_active_rank():
 
 
 @pytest.mark.parametrize("world", [1, 2, 4, 8, 6])
-def test_fused_ea(world):
+@pytest.mark.parametrize("variant", ["twoshot", "hybrid", "ll"])
+def test_fused_ea(world, variant):
     n, alpha = 40000, 0.2
     comm = _emu(world)
+    if variant == "ll":
+        if world == 1:
+            pytest.skip("a single rank has nobody to push to")
+        n = comm.ll_max_bytes // 4
     x_buf, x_views = comm.alloc_all(n)
     c0, c0_views = comm.alloc_all(n)
     c1, c1_views = comm.alloc_all(n)
@@ -148,7 +161,7 @@ def test_fused_ea(world):
         v.copy_(c)
     cur, nxt, cur_views, nxt_views = c0, c1, c0_views, c1_views
     for rnd in range(3):
-        comm.fused_ea(x_buf, cur, nxt, n, alpha, active=(1 << world) - 1, variant="twoshot", nblocks=5)
+        comm.fused_ea(x_buf, cur, nxt, n, alpha, active=(1 << world) - 1, variant=variant, nblocks=5)
         torch.cuda.synchronize()
         xs, c = oracle.elastic_average(xs, c, alpha)
         cur, nxt, cur_views, nxt_views = nxt, cur, nxt_views, cur_views
@@ -157,7 +170,7 @@ def test_fused_ea(world):
             torch.testing.assert_close(cur_views[r].cpu(), c, rtol=1e-5, atol=1e-6)
             assert torch.equal(cur_views[r], cur_views[0])
     # terminating drain round: nobody active -> nothing moves, next buffer mirrors the current one
-    comm.fused_ea(x_buf, cur, nxt, n, alpha, active=0, variant="twoshot", nblocks=5)
+    comm.fused_ea(x_buf, cur, nxt, n, alpha, active=0, variant=variant, nblocks=5)
     torch.cuda.synchronize()
     assert comm.result_of(0).n_active == 0
     for r in range(world):
@@ -166,10 +179,14 @@ def test_fused_ea(world):
 
 
 @pytest.mark.parametrize("world,root", [(1, 0), (2, 1), (4, 2), (8, 7), (8, 0), (5, 3), (3, 0)])
-@pytest.mark.parametrize("variant", ["oneshot", "twoshot"])
+@pytest.mark.parametrize("variant", ["oneshot", "twoshot", "ll"])
 def test_broadcast(world, root, variant):
     n = 30016
     comm = _emu(world)
+    if variant == "ll":
+        if world == 1:
+            pytest.skip("a single rank has nobody to push to")
+        n = comm.ll_max_bytes // 4
     a, a_views = comm.alloc_all(n)
     b, b_views = comm.alloc_all(n)
     for r, v in enumerate(a_views):
@@ -202,6 +219,63 @@ def test_back_to_back_collectives_keep_epochs_in_sync():
     want = float(sum(r + 19 for r in range(world)))
     for v in views:
         assert torch.all(v == want)
+
+
+def test_small_message_path_back_to_back_with_changing_sizes():
+    """The push path has no barrier: its safety rests on call-numbered flags and parity double buffering.  Many calls in a
+    row, sizes and grids changing, mixed with barrier-based calls on the same channel, all in one stream."""
+    world = 8
+    comm = _emu(world)
+    cap = comm.ll_max_bytes // 4
+    buf, views = comm.alloc_all(cap)
+    sizes = [cap, 64, cap // 2, 4, 1024, cap, 8]
+    for i in range(40):
+        n = sizes[i % len(sizes)]
+        for r, v in enumerate(views):
+            v[:n].fill_(float(r + i))
+        variant = "twoshot" if i % 7 == 3 else "ll"
+        comm.allreduce(buf, n, active=(1 << world) - 1, variant=variant, nblocks=1 + i % 3)
+        torch.cuda.synchronize()
+        want = float(sum(r + i for r in range(world)))
+        for v in views:
+            assert torch.all(v[:n] == want), f"call {i}, n {n}, variant {variant}"
+
+
+def test_contributor_count_reaches_the_host_without_a_copy():
+    """lua/AllReduceSGD.lua:20-29 returns n; here it is a LazyCount backed by a word in pinned host memory."""
+    import torch_distlearn_b200 as dl
+    world = 4
+    comm = _emu(world)
+    sgd = dl.AllReduceSGD(comm)
+    buf, views = comm.alloc_all(256)
+    for mask, want in [(0b1111, 4), (0b0101, 2), (0b0001, 1)]:
+        comm.allreduce(buf, 256, active=mask, normalize=True, variant="twoshot")
+        n = comm.lazy_count(0, comm.last_ticket)
+        assert int(n) == want and n == want and n + 1 == want + 1
+    comm.poll_error()      # nothing went wrong: must not raise
+
+
+def test_debug_mode_flags_an_impossible_epoch():
+    """DL_FLAG_DEBUG: a barrier slot may only hold the previous use of its parity or the current epoch."""
+    from torch_distlearn_b200 import _lib
+    comm = _emu(2, heap_mb=8)
+    comm.set_debug(True)
+    comm.set_timeout(2.0)
+    buf, views = comm.alloc_all(1024)
+    comm.allreduce(buf, 1024, active=0b11, variant="twoshot", nblocks=1)     # healthy: epochs 1, 2
+    torch.cuda.synchronize()
+    comm.poll_error()
+    # corrupt rank 0's slot for (parity 1, block 0, source 1): epoch 77 can never be there at barrier 3
+    pad = comm.heaps[0][:_lib.DL_PAD_BYTES].view(torch.int32)
+    slot = (1 * _lib.DL_MAX_BLOCKS + 0) * _lib.DL_MAX_RANKS + 1         # uint4 index into slots[2][blocks][ranks]
+    pad[slot * 4 + 0] = 77
+    pad[slot * 4 + 2] = 77
+    comm._c.emulate = 0        # play rank 0 alone, so nobody repairs the slot
+    with pytest.raises(_lib.NativeError):
+        comm.allreduce(buf, 1024, active=1, variant="twoshot", nblocks=1, read=True)
+    with pytest.raises(_lib.NativeError):
+        comm.poll_error()
+    comm.poll_error()          # reported once, then cleared
 
 
 @pytest.mark.parametrize("exclusive", [False, True])
@@ -273,3 +347,20 @@ def test_timeout_is_reported_not_hung():
     buf = comm.alloc(1024)
     with pytest.raises(_lib.NativeError):
         comm.allreduce(buf, 1024, active=1, variant="twoshot", nblocks=1, read=True)
+
+
+@pytest.mark.parametrize("world", [2, 8])
+def test_litmus_message_passing_and_store_buffering(world):
+    """The flag protocol's two shapes with random skew (csrc/litmus.cu).  On one GPU the ranks are emulated (one
+    cooperative launch), so this pins the code path and the GPU-scope behaviour; tests/run_multigpu.py runs the same
+    shapes across real GPUs over NVLink."""
+    comm = _emu(world, heap_mb=64)
+    iters = 20000
+    res = comm.litmus("mp", fenced=True, iterations=iters, nblocks=4)
+    for r in res:
+        assert r["timeouts"] == 0 and r["violations"] == 0 and r["checked"] == iters * 4 * 32
+    res = comm.litmus("sb", fenced=True, iterations=iters, nblocks=4)
+    loaded = torch.stack([r["loaded"] for r in res])          # [world, blocks, iterations]
+    assert all(r["timeouts"] == 0 for r in res)
+    forbidden = int((loaded.sum(0) == 0).sum())               # every rank of the ring loaded the old value
+    assert forbidden == 0, f"{forbidden} store-buffering violations with fence.sc.sys"

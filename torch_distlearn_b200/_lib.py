@@ -17,9 +17,13 @@ DL_MAX_BLOCKS = 160
 DL_NUM_CHANNELS = 4
 DL_PAD_BYTES = 256 * 1024
 DL_ETIMEOUT = -5
+DL_EPROTO = -6
+DL_FLAG_DEBUG = 1
+DL_HOST_RING = 64
 
-VARIANT_ONESHOT, VARIANT_TWOSHOT, VARIANT_NVLS = 0, 1, 2
-VARIANT_NAMES = {"oneshot": VARIANT_ONESHOT, "twoshot": VARIANT_TWOSHOT, "nvls": VARIANT_NVLS}
+VARIANT_ONESHOT, VARIANT_TWOSHOT, VARIANT_NVLS, VARIANT_LL, VARIANT_HYBRID = 0, 1, 2, 3, 4
+VARIANT_NAMES = {"oneshot": VARIANT_ONESHOT, "twoshot": VARIANT_TWOSHOT, "nvls": VARIANT_NVLS, "ll": VARIANT_LL,
+                 "hybrid": VARIANT_HYBRID}
 DT_F32, DT_I32, DT_I64, DT_F64 = 0, 1, 2, 3
 
 
@@ -28,10 +32,29 @@ class DlComm(C.Structure):
         ("rank", C.c_int32),
         ("world", C.c_int32),
         ("emulate", C.c_int32),
-        ("reserved", C.c_int32),
+        ("flags", C.c_uint32),
         ("base", C.c_void_p * DL_MAX_RANKS),
         ("mc", C.c_void_p),
         ("timeout_ns", C.c_uint64),
+        ("ll_off", C.c_uint64),
+        ("ll_slot_bytes", C.c_uint64),
+        ("host_words", C.c_void_p),
+        ("ticket", C.c_uint32),
+        ("nvls_permille", C.c_int32),
+    ]
+
+
+class _RingEntry(C.Structure):
+    _fields_ = [("ticket", C.c_uint32), ("n_active", C.c_uint32)]
+
+
+class DlHostWords(C.Structure):
+    """What the kernels leave in pinned host memory (include/distlearn_b200.h: dl_host_words_t)."""
+    _fields_ = [
+        ("error", C.c_uint32),
+        ("error_channel", C.c_uint32),
+        ("reserved", C.c_uint32 * 2),
+        ("ring", (_RingEntry * DL_HOST_RING) * DL_NUM_CHANNELS),
     ]
 
 
@@ -89,6 +112,10 @@ def cuda():
     _sig(lib, "dl_enable_peer", i32, [i32, i32])
     _sig(lib, "dl_can_access_peer", i32, [i32, i32, P(i32)])
     _sig(lib, "dl_memset_sync", i32, [i32, vp, i32, sz])
+    _sig(lib, "dl_litmus_scratch_bytes", sz, [i32, i32])
+    _sig(lib, "dl_litmus", i32, [cp, i32, i32, u64, i32, u32, i32, vp])
+    _sig(lib, "dl_host_words_alloc", i32, [P(vp), P(vp)])
+    _sig(lib, "dl_host_words_free", i32, [vp])
     _sig(lib, "dl_uds_listen", i32, [C.c_char_p, P(i32)])
     _sig(lib, "dl_uds_send_fd", i32, [C.c_char_p, i32, i32, i32])
     _sig(lib, "dl_uds_recv_fd", i32, [i32, P(i32), P(i32), i32])

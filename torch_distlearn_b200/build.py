@@ -33,6 +33,8 @@ CUDA_SOURCES = [
     "broadcast.cu",
     "async_ea.cu",
     "local_ops.cu",
+    "ll_ops.cu",
+    "litmus.cu",
     "tc_gemm.cu",
     "conv_ops.cu",
     "bn_ops.cu",

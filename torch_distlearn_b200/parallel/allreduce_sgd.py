@@ -53,11 +53,18 @@ class AllReduceSGD:
             self._stager.unpack(buf, tensors)
         self._last = ("allreduce", buf, n, None)
         self.steps += 1
-        self.last_n = res.n_active if res is not None else self.comm.world
+        if res is not None:
+            self.last_n = res.n_active
+        elif hasattr(self.comm, "lazy_count"):
+            # the kernel leaves n in pinned host memory; the value is fetched (event wait + plain load) when used
+            self.last_n = self.comm.lazy_count(self.channel, self.comm.last_ticket)
+        else:
+            self.last_n = self.comm.world
         return self.last_n
 
-    # Reading n back costs a host sync on the GPU backends; the reference returns it but no caller
-    # uses it.  Set ``want_contributors = True`` to get the exact count from every call.
+    # On the GPU backends the count comes back as a LazyCount: exact, but read only when it is used, so a caller
+    # that ignores it (every caller in the reference's examples) never synchronises.  Set ``want_contributors = True``
+    # to get a plain int from every call (one host synchronisation per call).
     want_contributors = False
 
     @property

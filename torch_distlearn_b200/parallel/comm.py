@@ -28,13 +28,61 @@ from typing import List, Optional
 import torch
 
 from .. import _lib
-from .._lib import DL_PAD_BYTES, DlComm, DlResult, VARIANT_NAMES, VARIANT_NVLS, VARIANT_ONESHOT, VARIANT_TWOSHOT
+from .._lib import (DL_PAD_BYTES, DlComm, DlHostWords, DlResult, VARIANT_HYBRID, VARIANT_LL, VARIANT_NAMES, VARIANT_NVLS,
+                    VARIANT_ONESHOT, VARIANT_TWOSHOT)
 
-VARIANT_TEXT = {VARIANT_ONESHOT: "oneshot", VARIANT_TWOSHOT: "twoshot", VARIANT_NVLS: "nvls"}
+VARIANT_TEXT = {VARIANT_ONESHOT: "oneshot", VARIANT_TWOSHOT: "twoshot", VARIANT_NVLS: "nvls", VARIANT_LL: "ll",
+                VARIANT_HYBRID: "hybrid"}
 _ALIGN = 512  # byte alignment of every symmetric allocation (>= 16 for 128-bit access)
 
 _DTYPE_CODES = {torch.float32: _lib.DT_F32, torch.int32: _lib.DT_I32, torch.int64: _lib.DT_I64,
                 torch.float64: _lib.DT_F64}
+
+
+class LazyCount:
+    """The contributor count ``n`` of a collective (lua/AllReduceSGD.lua:20: ``_, n = allReduce(...)``) as a value that
+    is read when it is USED.  The kernel leaves ``n`` in pinned host memory under this call's ticket; converting to
+    ``int`` waits for the event recorded behind the launch and reads that word — no device-to-host copy, and no
+    synchronisation at all for callers that never look at it.  Behaves like an int in arithmetic and comparisons."""
+
+    __slots__ = ("_comm", "_channel", "_ticket", "_event", "_value")
+
+    def __init__(self, comm, channel: int, ticket: int, event):
+        self._comm, self._channel, self._ticket, self._event, self._value = comm, channel, ticket, event, None
+
+    def __int__(self) -> int:
+        if self._value is None:
+            if self._event is not None:
+                self._event.synchronize()
+            self._value = self._comm._read_ring(self._channel, self._ticket)
+            self._comm.poll_error()
+        return self._value
+
+    __index__ = __int__
+
+    def __repr__(self) -> str:
+        return str(int(self))
+
+    def __eq__(self, other):
+        return int(self) == other
+
+    def __hash__(self):
+        return hash(int(self))
+
+    def __lt__(self, other): return int(self) < other
+    def __le__(self, other): return int(self) <= other
+    def __gt__(self, other): return int(self) > other
+    def __ge__(self, other): return int(self) >= other
+    def __add__(self, other): return int(self) + other
+    __radd__ = __add__
+    def __sub__(self, other): return int(self) - other
+    def __rsub__(self, other): return other - int(self)
+    def __mul__(self, other): return int(self) * other
+    __rmul__ = __mul__
+    def __truediv__(self, other): return int(self) / other
+    def __rtruediv__(self, other): return other / int(self)
+    def __bool__(self): return int(self) != 0
+    def __float__(self): return float(int(self))
 
 
 @dataclass
@@ -75,10 +123,18 @@ class _VariantTable:
     that ``bench/sweep.py`` writes (``variant_table.json``); ``DL_B200_VARIANT`` forces one."""
 
     DEFAULT = {"allreduce": 512 * 1024, "fused_sgd": 512 * 1024, "broadcast": 256 * 1024}
+    OPS = ("allreduce", "fused_sgd", "fused_ea", "broadcast")
 
     def __init__(self, world: int = 8):
         self.oneshot_max = dict(self.DEFAULT)
-        self.nvls_min = {"allreduce": 0, "fused_sgd": 0, "fused_ea": 0, "broadcast": 0}
+        self.nvls_min = {op: 0 for op in self.OPS}
+        # ll_max: largest message that takes the push/no-barrier path (capped by the staging area the communicator
+        # could afford); hybrid_min: smallest message that takes the pipelined switch+P2P kernel (broadcast has
+        # none); hybrid_permille: share of every slice reduced in the switch (needs multicast; 0 = all P2P)
+        self.ll_max = {op: 64 * 1024 for op in self.OPS}
+        self.hybrid_min = {"allreduce": 1 << 20, "fused_sgd": 1 << 20, "fused_ea": 1 << 20}
+        self.hybrid_permille = {op: (750 if world > 2 else 0) for op in self.OPS}
+        self.source = "defaults"
         path = os.environ.get("DL_B200_VARIANT_TABLE") or os.path.join(os.path.dirname(__file__), "variant_table.json")
         if os.path.exists(path):
             try:
@@ -87,13 +143,22 @@ class _VariantTable:
                 if keys:      # per-world tables: take the smallest measured world >= ours (else the largest)
                     pick = next((k for k in keys if k >= world), keys[-1])
                     data = data[str(pick)]
-                self.oneshot_max.update(data.get("oneshot_max", {}))
-                self.nvls_min.update(data.get("nvls_min", {}))
-            except Exception:
-                pass
+                for field in ("oneshot_max", "nvls_min", "ll_max", "hybrid_min", "hybrid_permille"):
+                    entry = data.get(field, {})
+                    if not isinstance(entry, dict):
+                        raise ValueError(f"{field} must be an object")
+                    getattr(self, field).update({k: int(v) for k, v in entry.items()})
+                self.source = path
+            except (OSError, ValueError, TypeError, KeyError) as e:
+                # a damaged table must not pass silently for a measured one: say so once, keep the defaults
+                import warnings
+                warnings.warn(f"distlearn_b200: ignoring variant table {path}: {e!r}; using built-in defaults")
         self.forced = os.environ.get("DL_B200_VARIANT")
+        if os.environ.get("DL_B200_NVLS_PERMILLE"):
+            self.hybrid_permille = {op: int(os.environ["DL_B200_NVLS_PERMILLE"]) for op in self.OPS}
 
-    def pick(self, op: str, nbytes: int, world: int, has_mc: bool, requested: str = "auto") -> int:
+    def pick(self, op: str, nbytes: int, world: int, has_mc: bool, requested: str = "auto", ll_cap: int = 0,
+             aligned32: bool = False) -> int:
         req = self.forced or requested
         if req and req != "auto":
             v = VARIANT_NAMES[req]
@@ -101,12 +166,23 @@ class _VariantTable:
                 v = VARIANT_TWOSHOT
             if op == "fused_ea" and v == VARIANT_ONESHOT:
                 v = VARIANT_TWOSHOT
+            if v == VARIANT_LL and nbytes > ll_cap:
+                v = VARIANT_TWOSHOT
+            if v == VARIANT_HYBRID and (not aligned32 or op == "broadcast"):
+                v = VARIANT_NVLS if (has_mc and world > 2) else VARIANT_TWOSHOT
             return v
+        if world > 1 and nbytes <= min(self.ll_max.get(op, 0), ll_cap):
+            return VARIANT_LL
         if op != "fused_ea" and nbytes <= self.oneshot_max.get(op, 0):
             return VARIANT_ONESHOT
+        if world > 1 and aligned32 and op in self.hybrid_min and nbytes >= self.hybrid_min[op]:
+            return VARIANT_HYBRID
         if has_mc and world > 2 and nbytes >= self.nvls_min.get(op, 0):
             return VARIANT_NVLS
         return VARIANT_TWOSHOT
+
+    def permille(self, op: str, has_mc: bool) -> int:
+        return max(0, min(1000, self.hybrid_permille.get(op, 0))) if has_mc else 0
 
 
 class Communicator:
@@ -150,10 +226,12 @@ class Communicator:
     def _mk_result(self, res: DlResult) -> CommResult:
         return CommResult(int(res.n_active), [int(res.payload[r]) for r in range(self.world)])
 
-    def pick_variant(self, op: str, nbytes: int, requested: str = "auto") -> int:
-        return self._variants.pick(op, nbytes, self.world, self.has_multicast, requested)
+    def pick_variant(self, op: str, nbytes: int, requested: str = "auto", offsets=(), n: int = 8) -> int:
+        aligned32 = n % 8 == 0 and all(o % 32 == 0 for o in offsets)
+        return self._variants.pick(op, nbytes, self.world, self.has_multicast, requested, self.ll_max_bytes, aligned32)
 
     has_multicast = False
+    ll_max_bytes = 0            # largest message the small-message staging area can take (0: none)
 
     def close(self) -> None:
         pass
@@ -311,15 +389,78 @@ class _CudaOps(Communicator):
         self._c = DlComm()
         self._c.rank, self._c.world, self._c.emulate = rank, world, 0
         self._c.timeout_ns = int(float(os.environ.get("DL_B200_TIMEOUT_S", "20")) * 1e9)
+        if os.environ.get("DL_B200_DEBUG", "0") == "1":
+            self._c.flags |= _lib.DL_FLAG_DEBUG
         self._res = DlResult()
+        self._ticket = 0
+        self._host_words = None
+        self._host_ptr = None
+        hp, dp = C.c_void_p(), C.c_void_p()
+        with torch.cuda.device(device):
+            _lib.check(self._lib.dl_host_words_alloc(C.byref(hp), C.byref(dp)))
+        self._host_ptr = hp.value
+        self._host_words = DlHostWords.from_address(hp.value)
+        self._c.host_words = dp.value
 
     def _nb(self, nblocks: int) -> int:
         return nblocks if nblocks else self.max_blocks
+
+    # -- small-message staging, tickets, errors ---------------------------------------------------------
+    def _setup_ll(self) -> None:
+        """Carve the DL_VARIANT_LL staging area out of the heap (first allocation: same offset on every rank).  It has
+        to take twice the payload per (channel, parity, source); the limit shrinks with small heaps."""
+        if self.world < 2:
+            return
+        limit = int(float(os.environ.get("DL_B200_LL_MAX_KB", "64")) * 1024)
+        budget = self.heap_bytes // 8
+        slots = _lib.DL_NUM_CHANNELS * 2 * self.world
+        while limit >= 4096 and slots * (2 * limit + 512) > budget:
+            limit //= 2
+        if limit < 4096:
+            return
+        slot_bytes = _round_up(2 * limit + 16, 512)
+        buf = self.alloc(slots * slot_bytes // 4, torch.float32, "ll.staging")
+        self._c.ll_off, self._c.ll_slot_bytes = buf.offset, slot_bytes
+        self.ll_max_bytes = limit
+
+    def set_debug(self, on: bool = True) -> None:
+        """Barriers check that every slot holds an epoch the protocol can produce (DL_EPROTO otherwise)."""
+        self._c.flags = (self._c.flags | _lib.DL_FLAG_DEBUG) if on else (self._c.flags & ~_lib.DL_FLAG_DEBUG)
+
+    def _begin(self, op: str) -> int:
+        self._ticket = (self._ticket + 1) & 0xFFFFFFFF
+        self._c.ticket = self._ticket
+        self._c.nvls_permille = self._variants.permille(op, self.has_multicast)
+        return self._ticket
+
+    def _read_ring(self, channel: int, ticket: int) -> int:
+        e = self._host_words.ring[channel][ticket % _lib.DL_HOST_RING]
+        if e.ticket != ticket:
+            raise RuntimeError("contributor count no longer available: read it within "
+                               f"{_lib.DL_HOST_RING} collectives of the call that produced it")
+        return int(e.n_active)
+
+    def lazy_count(self, channel: int, ticket: int, stream=None) -> LazyCount:
+        ev = torch.cuda.Event()
+        ev.record(stream if stream is not None else torch.cuda.current_stream(self.device))
+        return LazyCount(self, channel, ticket, ev)
+
+    def poll_error(self) -> None:
+        """Raise if any kernel of this communicator gave up waiting for a peer.  A plain read of pinned host memory —
+        cheap enough for every step.  The word is sticky on the device side; reporting clears it."""
+        hw = self._host_words
+        if hw is not None and hw.error:
+            code, ch = int(hw.error), int(hw.error_channel)
+            hw.error = 0
+            what = "timed out waiting for a peer" if code == -_lib.DL_ETIMEOUT else "found a barrier slot the protocol cannot produce"
+            raise _lib.NativeError(-code, f"a collective on channel {ch} {what} (rank {self.rank} of {self.world}); "
+                                          "replicas may have diverged: re-synchronise the parameters")
 
     def set_timeout(self, seconds: float) -> None:
         self._c.timeout_ns = int(seconds * 1e9)
 
     def barrier(self, active: int = 1, payload: int = 0, channel: int = 0, read: bool = True, stream=None):
+        self.last_ticket = self._begin("barrier")
         with torch.cuda.device(self.device):
             _lib.check(self._lib.dl_barrier(C.byref(self._c), int(active), int(payload), channel, _stream_ptr(self.device, stream)))
             self.launches += 1
@@ -330,9 +471,10 @@ class _CudaOps(Communicator):
                   stream=None):
         n = buf.numel if n is None else n
         nbytes = n * buf.tensor.element_size()
-        v = self.pick_variant("allreduce", nbytes, variant)
-        if buf.dtype != torch.float32 and v != VARIANT_ONESHOT:
+        v = self.pick_variant("allreduce", nbytes, variant, (buf.offset,), n)
+        if buf.dtype != torch.float32 and v not in (VARIANT_ONESHOT, VARIANT_LL):
             v = VARIANT_ONESHOT
+        self.last_ticket = self._begin("allreduce")
         with torch.cuda.device(self.device), _Range(f"distlearn.allreduce[{VARIANT_TEXT[v]}]"):
             _lib.check(self._lib.dl_allreduce(C.byref(self._c), _DTYPE_CODES[buf.dtype], buf.offset, n, v, int(active),
                                               int(payload), int(normalize), self._nb(nblocks), channel,
@@ -344,7 +486,9 @@ class _CudaOps(Communicator):
                   momentum: float = 0.0, weight_decay: float = 0.0, nesterov: bool = False, active: int = 1,
                   payload: int = 0, zero_grads: bool = True, variant: str = "auto", channel: int = 0, read: bool = False,
                   nblocks: int = 0, stream=None):
-        v = self.pick_variant("fused_sgd", n * 4, variant)
+        v = self.pick_variant("fused_sgd", n * 4, variant,
+                              (grads.offset, params.offset, momentum_buf.offset if momentum_buf else 0), n)
+        self.last_ticket = self._begin("fused_sgd")
         with torch.cuda.device(self.device), _Range(f"distlearn.fused_sgd[{VARIANT_TEXT[v]}]"):
             _lib.check(self._lib.dl_fused_sgd(C.byref(self._c), grads.offset, params.offset,
                                               momentum_buf.offset if momentum_buf else 0, n, lr, momentum, weight_decay,
@@ -356,7 +500,8 @@ class _CudaOps(Communicator):
     def fused_ea(self, x: SymBuffer, c_cur: SymBuffer, c_next: SymBuffer, n: int, alpha: float, active: int = 1,
                  payload: int = 0, variant: str = "auto", channel: int = 0, read: bool = False, nblocks: int = 0,
                  stream=None):
-        v = self.pick_variant("fused_ea", n * 4, variant)
+        v = self.pick_variant("fused_ea", n * 4, variant, (x.offset, c_cur.offset, c_next.offset), n)
+        self.last_ticket = self._begin("fused_ea")
         with torch.cuda.device(self.device), _Range(f"distlearn.fused_ea[{VARIANT_TEXT[v]}]"):
             _lib.check(self._lib.dl_fused_ea(C.byref(self._c), x.offset, c_cur.offset, c_next.offset, n, alpha, v,
                                              int(active), int(payload), self._nb(nblocks), channel,
@@ -368,7 +513,8 @@ class _CudaOps(Communicator):
                   payload: int = 0, variant: str = "auto", channel: int = 0, read: bool = False, nblocks: int = 0,
                   stream=None):
         n = buf.numel if n is None else n
-        v = self.pick_variant("broadcast", n * 4, variant)
+        v = self.pick_variant("broadcast", n * 4, variant, (buf.offset, also.offset if also else 0), n)
+        self.last_ticket = self._begin("broadcast")
         with torch.cuda.device(self.device), _Range(f"distlearn.broadcast[{VARIANT_TEXT[v]}]"):
             _lib.check(self._lib.dl_broadcast(C.byref(self._c), buf.offset, also.offset if also else 0, n, root, v,
                                               int(payload), self._nb(nblocks), channel, _stream_ptr(self.device, stream)))
@@ -416,6 +562,43 @@ class _CudaOps(Communicator):
     def synchronize(self) -> None:
         torch.cuda.synchronize(self.device)
 
+    # -- memory-model litmus tests (csrc/litmus.cu) ---------------------------------------------------------
+    def litmus(self, shape: str = "mp", fenced: bool = True, iterations: int = 100000, nblocks: int = 8, seed: int = 1):
+        """Run the message-passing ("mp") or store-buffering ("sb") litmus shape across the ranks of this communicator
+        (collective call).  Returns ``{"checked", "violations", "timeouts"}`` for this rank; for "sb" also ``"loaded"``,
+        an int32 tensor [nblocks, iterations] of the values this rank loaded (the forbidden outcome — every rank of the
+        ring loading 0 in the same iteration — is judged by the caller, who can see all ranks)."""
+        which = {"mp": 0, "sb": 1}[shape]
+        nbytes = int(self._lib.dl_litmus_scratch_bytes(iterations, nblocks))
+        key = (iterations, nblocks)
+        cache = self.__dict__.setdefault("_litmus_scratch", {})
+        if key not in cache:
+            cache[key] = self.alloc((nbytes + 3) // 4, torch.int32, "litmus")
+        buf = cache[key]
+        views = [h[buf.offset:buf.offset + buf.numel * 4].view(torch.int32) for h in self.heaps] if hasattr(self, "heaps") else [buf.tensor]
+        for v in views:
+            v.zero_()
+        torch.cuda.synchronize(self.device)
+        if hasattr(self, "_host_barrier"):
+            self._host_barrier()
+        with torch.cuda.device(self.device):
+            _lib.check(self._lib.dl_litmus(C.byref(self._c), which, int(fenced), buf.offset, iterations, seed & 0xFFFFFFFF, nblocks,
+                                           _stream_ptr(self.device)))
+        torch.cuda.synchronize(self.device)
+        self.launches += 1
+        out = []
+        for v in views:
+            counts = v[:16].view(torch.int64).cpu()
+            d = {"checked": int(counts[0]), "violations": int(counts[1]), "timeouts": int(counts[2])}
+            if which == 1:
+                per_block = (512 + 8 * iterations) // 4
+                body = v[16:16 + per_block * nblocks].view(nblocks, per_block)
+                d["loaded"] = body[:, 128 + iterations:128 + 2 * iterations].cpu()
+            out.append(d)
+        if hasattr(self, "_host_barrier"):
+            self._host_barrier()
+        return out if hasattr(self, "heaps") else out[0]
+
 
 class P2PCommunicator(_CudaOps):
     """One process per GPU; heaps mapped across processes (VMM + fd passing, multicast if
@@ -457,6 +640,7 @@ class P2PCommunicator(_CudaOps):
                 raise RuntimeError("torch.distributed must be initialised to bootstrap a multi-rank P2PCommunicator")
             self._bootstrap(mode, use_multicast)
         _lib.check(self._lib.dl_reset_pad(C.byref(self._c)))
+        self._setup_ll()
         self._host_barrier()
 
     # -- bootstrap ----------------------------------------------------------------------------------
@@ -641,11 +825,55 @@ class P2PCommunicator(_CudaOps):
                 "mc_error": getattr(self, "_mc_error", None), "vmm_error": getattr(self, "_vmm_error", None)}
 
     def close(self) -> None:
-        # Mappings are released by process exit; explicit teardown keeps long-lived processes clean.
+        """Collective teardown: wait for the device, make sure no peer still uses our memory, then drop every mapping
+        this process made — the multicast view and binding, the peers' heaps, our own heap, the cudaIpc imports — and
+        release the handles, so a long-lived process that creates communicators repeatedly does not leak address space
+        or physical memory.  Tensors that alias the heap (FlatParams views) must not be used afterwards."""
+        if getattr(self, "_closed", False):
+            return
+        self._closed = True
         try:
             torch.cuda.synchronize(self.device)
         except Exception:  # noqa: BLE001
             pass
+        if self.world > 1:
+            try:
+                self._dist.barrier(group=self._group)      # nobody is still reading or writing a peer heap
+            except Exception:  # noqa: BLE001
+                pass
+        lib = self._lib
+        self._bytes = None
+        if self.mode == "vmm":
+            if self._mc_handle is not None:
+                if self._c.mc:
+                    lib.dl_vmm_unmap(self._c.mc, self.heap_bytes)
+                lib.dl_mc_unbind(self._mc_handle, self._dev, self.heap_bytes)
+                lib.dl_vmm_release(self._mc_handle)
+                self._mc_handle = None
+            self._teardown_vmm()
+        elif self.mode == "ipc":
+            for q in self._ipc_ptrs:
+                lib.dl_ipc_close(q)
+            self._ipc_ptrs = []
+            if self.world > 1:
+                try:
+                    self._dist.barrier(group=self._group)  # every importer has closed before the owner frees
+                except Exception:  # noqa: BLE001
+                    pass
+            if getattr(self, "_ipc_local", None):
+                lib.dl_ipc_free(self._ipc_local)
+                self._ipc_local = None
+        else:
+            self._heap_tensor = None
+        for r in range(self.world):
+            self._c.base[r] = None
+        self._c.mc = None
+        self.has_multicast = False
+        if self._host_ptr:
+            self._c.host_words = None
+            self._host_words = None
+            lib.dl_host_words_free(self._host_ptr)
+            self._host_ptr = None
 
 
 class EmulatedCommunicator(_CudaOps):
@@ -664,6 +892,7 @@ class EmulatedCommunicator(_CudaOps):
         for r in range(world):
             self._c.base[r] = self.heaps[r].data_ptr()
         _lib.check(self._lib.dl_reset_pad(C.byref(self._c)))
+        self._setup_ll()
 
     def _local_bytes(self) -> torch.Tensor:
         return self.heaps[0]
