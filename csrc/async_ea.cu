@@ -18,6 +18,7 @@
 
 struct AsyncArgs {
   float* x;
+  float* x_out;  // where the moved parameters go: x itself, or a second buffer when x must stay intact
   uint64_t c_off;
   unsigned long long n;
   float alpha;
@@ -39,14 +40,34 @@ __global__ void __launch_bounds__(DL_THREADS, 1) async_ea_client_kernel(dl_comm_
       if (blockIdx.x == 0) {
         unsigned int ticket;
         asm volatile("atom.relaxed.sys.global.add.u32 %0, [%1], 1;" : "=r"(ticket) : "l"(&srv->ticket_next) : "memory");
-        loc->local_ticket = ticket;
-        while (dl_ld_acquire_sys_u32(&srv->ticket_serving) != ticket) {
+        // Nobody ever walks away from the queue, and nobody can block it for good.  If the ticket being served does
+        // not change for a whole timeout its holder is taken for dead and ONE waiter passes that turn on (CAS); a
+        // waiter that finds itself overtaken by such a recovery draws a new ticket.  A holder that was only slow then
+        // shares the center with its successor for a moment — the lock-free mode's semantics, exact all the same
+        // because the center is only ever changed by atomic adds.  Releases never move the counter backwards (max).
+        unsigned int last = 0xffffffffu;
+        int recoveries = 0;
+        while (true) {
+          const unsigned int cur = dl_ld_acquire_sys_u32(&srv->ticket_serving);
+          if (cur == ticket) break;
+          if (static_cast<int>(cur - ticket) > 0) {  // overtaken: queue again
+            asm volatile("atom.relaxed.sys.global.add.u32 %0, [%1], 1;" : "=r"(ticket) : "l"(&srv->ticket_next) : "memory");
+            last = 0xffffffffu;
+            continue;
+          }
+          if (cur != last) { last = cur; t0 = 0; polls = 0; }
           if ((++polls & 1023u) == 0u) {
             const unsigned long long now = dl_globaltimer();
             if (t0 == 0) t0 = now;
-            if (now - t0 > limit) { ok = 0; break; }
+            if (now - t0 > limit) {
+              if (++recoveries > 8) { ok = 0; break; }   // the server's memory itself is not answering
+              unsigned int seen;
+              asm volatile("atom.relaxed.sys.global.cas.b32 %0, [%1], %2, %3;" : "=r"(seen) : "l"(&srv->ticket_serving), "r"(cur), "r"(cur + 1u) : "memory");
+              t0 = 0;
+            }
           }
         }
+        loc->local_ticket = ticket;
         dl_st_release_gpu_u32(&loc->local_go, ok ? 1u : 2u);
       } else {
         unsigned int g;
@@ -74,6 +95,7 @@ __global__ void __launch_bounds__(DL_THREADS, 1) async_ea_client_kernel(dl_comm_
     const unsigned long long stride = static_cast<unsigned long long>(gridDim.x) * DL_THREADS;
     float4* center = dl_at<float4>(c, a.server, a.c_off);
     float4* x4 = reinterpret_cast<float4*>(a.x);
+    float4* xo4 = reinterpret_cast<float4*>(a.x_out);
     const float alpha = a.alpha;
     for (unsigned long long i0 = static_cast<unsigned long long>(blockIdx.x) * DL_THREADS + threadIdx.x; i0 < n4;
          i0 += stride * U) {
@@ -94,7 +116,7 @@ __global__ void __launch_bounds__(DL_THREADS, 1) async_ea_client_kernel(dl_comm_
           d.x = (xv[u].x - cv[u].x) * alpha; d.y = (xv[u].y - cv[u].y) * alpha;
           d.z = (xv[u].z - cv[u].z) * alpha; d.w = (xv[u].w - cv[u].w) * alpha;
           xv[u].x -= d.x; xv[u].y -= d.y; xv[u].z -= d.z; xv[u].w -= d.w;
-          x4[idx] = xv[u];
+          xo4[idx] = xv[u];
           dl_red_add_f4_sys(center + idx, d);
         }
       }
@@ -105,7 +127,7 @@ __global__ void __launch_bounds__(DL_THREADS, 1) async_ea_client_kernel(dl_comm_
          i += stride) {
       const float cvs = *reinterpret_cast<volatile float*>(cs + i);
       const float d = (a.x[i] - cvs) * alpha;
-      a.x[i] -= d;
+      a.x_out[i] = a.x[i] - d;
       asm volatile("red.relaxed.sys.global.add.f32 [%0], %1;" ::"l"(cs + i), "f"(d) : "memory");
     }
   }
@@ -118,7 +140,8 @@ __global__ void __launch_bounds__(DL_THREADS, 1) async_ea_client_kernel(dl_comm_
       __threadfence_system();
       if (a.exclusive && ok) {
         const unsigned int ticket = loc->local_ticket;
-        dl_st_release_sys_u32(&srv->ticket_serving, ticket + 1u);
+        unsigned int prev_serving;
+        asm volatile("atom.release.sys.global.max.u32 %0, [%1], %2;" : "=r"(prev_serving) : "l"(&srv->ticket_serving), "r"(ticket + 1u) : "memory");
       }
       if (ok) {
         asm volatile("red.release.sys.global.add.u64 [%0], 1;" ::"l"(&srv->sync_count) : "memory");
@@ -133,15 +156,21 @@ __global__ void __launch_bounds__(DL_THREADS, 1) async_ea_client_kernel(dl_comm_
 
 extern "C" int dl_async_ea_client(const dl_comm_t* c, int server, float* x, uint64_t c_off, uint64_t n, float alpha,
                                   int exclusive, int nblocks, void* stream) {
+  return dl_async_ea_client_out(c, server, x, x, c_off, n, alpha, exclusive, nblocks, stream);
+}
+
+extern "C" int dl_async_ea_client_out(const dl_comm_t* c, int server, float* x, float* x_out, uint64_t c_off, uint64_t n,
+                                      float alpha, int exclusive, int nblocks, void* stream) {
   int nb = dl_check_comm(c, 0, dl_pick_blocks(n / 4 + 1, 4, nblocks));
   if (nb < 0) return nb;
   DL_REQUIRE(server >= 0 && server < c->world, "dl_async_ea_client: bad server rank %d", server);
   DL_REQUIRE(x != nullptr && reinterpret_cast<uintptr_t>(x) % 16 == 0, "dl_async_ea_client: x must be 16-byte aligned");
+  DL_REQUIRE(x_out != nullptr && reinterpret_cast<uintptr_t>(x_out) % 16 == 0, "dl_async_ea_client: x_out must be 16-byte aligned");
   DL_REQUIRE(c_off % 16 == 0 && c_off >= DL_PAD_BYTES, "dl_async_ea_client: bad center offset");
   // exclusive mode spins between blocks of one grid: they must all be resident
   if (exclusive && nb > dl_sm_count()) nb = dl_sm_count();
   AsyncArgs a;
-  a.x = x; a.c_off = c_off; a.n = n; a.alpha = alpha; a.server = server; a.exclusive = exclusive;
+  a.x = x; a.x_out = x_out; a.c_off = c_off; a.n = n; a.alpha = alpha; a.server = server; a.exclusive = exclusive;
   async_ea_client_kernel<<<nb, DL_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(*c, a);
   dl_note_launch();
   DL_CUDA(cudaGetLastError());

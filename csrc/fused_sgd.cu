@@ -264,7 +264,7 @@ __global__ void __launch_bounds__(DL_THREADS, 1) sgd_oneshot_kernel(dl_comm_t c,
 
 // ---- world == 1 and helper ops: no communication ---------------------------------------------
 struct LocalSgdArgs {
-  float* p; float* g; float* m;
+  float* p; const float* p_in; float* g; float* m;
   unsigned long long n;
   float lr, momentum, wd, scale;
   int nesterov, zero_grads;
@@ -276,18 +276,19 @@ __global__ void __launch_bounds__(DL_THREADS) local_sgd_kernel(LocalSgdArgs a) {
   SgdArgs s{};
   s.lr = a.lr; s.momentum = a.momentum; s.wd = a.wd; s.nesterov = a.nesterov;
   float4* p4 = reinterpret_cast<float4*>(a.p);
+  const float4* pi4 = reinterpret_cast<const float4*>(a.p_in);
   float4* g4 = reinterpret_cast<float4*>(a.g);
   float4* m4 = reinterpret_cast<float4*>(a.m);
   for (unsigned long long i = static_cast<unsigned long long>(blockIdx.x) * DL_THREADS + threadIdx.x; i < n4;
        i += stride) {
     const float4 g = dl_scale(g4[i], a.scale);
-    p4[i] = sgd_update(g, p4[i], m4 ? m4 + i : nullptr, s);
+    p4[i] = sgd_update(g, pi4[i], m4 ? m4 + i : nullptr, s);
     if (a.zero_grads) g4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
   }
   // scalar tail (n not a multiple of 4)
   for (unsigned long long i = n4 * 4 + static_cast<unsigned long long>(blockIdx.x) * DL_THREADS + threadIdx.x;
        i < a.n; i += stride) {
-    a.p[i] = sgd_update1(__fmul_rn(a.g[i], a.scale), a.p[i], a.m ? a.m + i : nullptr, s);
+    a.p[i] = sgd_update1(__fmul_rn(a.g[i], a.scale), a.p_in[i], a.m ? a.m + i : nullptr, s);
     if (a.zero_grads) a.g[i] = 0.f;
   }
 }
@@ -360,12 +361,18 @@ extern "C" int dl_fused_sgd(const dl_comm_t* c, uint64_t g_off, uint64_t p_off, 
 extern "C" int dl_local_sgd(float* p, float* g, float* m, uint64_t n, float lr, float momentum,
                             float weight_decay, int nesterov, float grad_scale, int zero_grads,
                             void* stream) {
-  DL_REQUIRE(p && g, "dl_local_sgd: null pointer");
-  DL_REQUIRE((reinterpret_cast<uintptr_t>(p) | reinterpret_cast<uintptr_t>(g) | reinterpret_cast<uintptr_t>(m)) % 16 == 0,
+  return dl_local_sgd_from(p, p, g, m, n, lr, momentum, weight_decay, nesterov, grad_scale, zero_grads, stream);
+}
+
+extern "C" int dl_local_sgd_from(float* p, const float* p_in, float* g, float* m, uint64_t n, float lr, float momentum,
+                                 float weight_decay, int nesterov, float grad_scale, int zero_grads, void* stream) {
+  DL_REQUIRE(p && g && p_in, "dl_local_sgd: null pointer");
+  DL_REQUIRE((reinterpret_cast<uintptr_t>(p) | reinterpret_cast<uintptr_t>(p_in) | reinterpret_cast<uintptr_t>(g) |
+              reinterpret_cast<uintptr_t>(m)) % 16 == 0,
              "dl_local_sgd: pointers must be 16-byte aligned");
   if (n == 0) return DL_OK;
   LocalSgdArgs a;
-  a.p = p; a.g = g; a.m = m; a.n = n; a.lr = lr; a.momentum = momentum; a.wd = weight_decay;
+  a.p = p; a.p_in = p_in; a.g = g; a.m = m; a.n = n; a.lr = lr; a.momentum = momentum; a.wd = weight_decay;
   a.scale = grad_scale; a.nesterov = nesterov; a.zero_grads = zero_grads;
   const int nb = dl_pick_blocks(n / 4 + 1, 2, 0);
   local_sgd_kernel<<<nb, DL_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(a);

@@ -565,24 +565,39 @@ int dlh_async_ea_client(void* handle, int server, float* x, uint64_t c_off, uint
   HostPad* srv = h->pad(server);
   uint32_t ticket = 0;
   if (exclusive) {
+    // Same queue discipline as the CUDA kernel (csrc/async_ea.cu): nobody leaves the queue; a ticket that is not
+    // released for a whole timeout is passed on by one of the waiters (its holder is taken for dead), a waiter that
+    // was overtaken queues again, releases never move the counter backwards.
     ticket = srv->ticket_next.fetch_add(1, std::memory_order_relaxed);
+    uint32_t last = 0xffffffffu;
+    int recoveries = 0;
     Spinner sp(h->timeout_s);
-    while (srv->ticket_serving.load(std::memory_order_acquire) != ticket) {
+    while (true) {
+      uint32_t cur = srv->ticket_serving.load(std::memory_order_acquire);
+      if (cur == ticket) break;
+      if (static_cast<int32_t>(cur - ticket) > 0) {
+        ticket = srv->ticket_next.fetch_add(1, std::memory_order_relaxed);
+        last = 0xffffffffu;
+        continue;
+      }
+      if (cur != last) {
+        last = cur;
+        sp = Spinner(h->timeout_s);
+      }
       if (!sp.wait_more()) {
-        set_error("timed out waiting for the center lock (ticket %u)", ticket);
-        return DL_ETIMEOUT;
+        if (++recoveries > 8) {
+          set_error("timed out waiting for the center lock (ticket %u)", ticket);
+          return DL_ETIMEOUT;
+        }
+        srv->ticket_serving.compare_exchange_strong(cur, cur + 1u, std::memory_order_acq_rel);
+        sp = Spinner(h->timeout_s);
       }
     }
   }
   float* center = h->at<float>(server, c_off);
-  if (exclusive) {
-    for (uint64_t i = 0; i < n; ++i) {
-      const float d = (x[i] - center[i]) * alpha;
-      x[i] -= d;
-      center[i] += d;
-    }
-    srv->ticket_serving.store(ticket + 1u, std::memory_order_release);
-  } else {
+  {
+    // the center is only ever changed by atomic adds, with or without the lock: a recovery that lets a slow holder and
+    // its successor overlap cannot lose an update
     for (uint64_t i = 0; i < n; ++i) {
       std::atomic<uint32_t>* cell = reinterpret_cast<std::atomic<uint32_t>*>(center + i);
       uint32_t old_bits = cell->load(std::memory_order_relaxed);
@@ -601,7 +616,22 @@ int dlh_async_ea_client(void* handle, int server, float* x, uint64_t c_off, uint
       }
     }
   }
+  if (exclusive) {  // release: serving = max(serving, ticket + 1)
+    uint32_t cur = srv->ticket_serving.load(std::memory_order_relaxed);
+    while (static_cast<int32_t>(ticket + 1u - cur) > 0 &&
+           !srv->ticket_serving.compare_exchange_weak(cur, ticket + 1u, std::memory_order_release, std::memory_order_relaxed)) {
+    }
+  }
   srv->sync_count.fetch_add(1, std::memory_order_release);
+  return DL_OK;
+}
+
+// Fault injection for the tests: draw a ticket of the exclusive-mode queue and never release it (a client that died
+// while holding the center lock).
+int dlh_debug_take_ticket(void* handle, int server, uint32_t* ticket) {
+  Handle* h = static_cast<Handle*>(handle);
+  if (!h || server < 0 || server >= h->world || !ticket) return DL_EINVAL;
+  *ticket = h->pad(server)->ticket_next.fetch_add(1, std::memory_order_relaxed);
   return DL_OK;
 }
 

@@ -195,6 +195,12 @@ int dl_reset_pad(const dl_comm_t* c);
  * x is a plain device pointer; the center lives at c_off in the server heap. */
 int dl_async_ea_client(const dl_comm_t* c, int server, float* x, uint64_t c_off, uint64_t n,
                        float alpha, int exclusive, int nblocks, void* stream);
+/* Same, but the moved parameters x - d are written to x_out and x is left untouched.  d depends only on x and the
+ * center, so a trainer can run the sync on a side stream UNDER the forward/backward pass that still reads x, and apply
+ * the gradient afterwards from x_out (dl_local_sgd_from): the reference's order "gradient at x, elastic move, apply
+ * the gradient" (examples/EASGD_client.lua:106-117) with the exchange hidden behind the compute. */
+int dl_async_ea_client_out(const dl_comm_t* c, int server, float* x, float* x_out, uint64_t c_off, uint64_t n,
+                           float alpha, int exclusive, int nblocks, void* stream);
 /* Copy n floats from `src_rank`'s heap at off into dst (P2P loads): initClient /
  * startTest center pull (lua/AsyncEA.lua:64-78, :268-285). */
 int dl_peer_pull(const dl_comm_t* c, int src_rank, uint64_t off, float* dst, uint64_t n,
@@ -277,6 +283,9 @@ int dl_head_bwd(const float* feat, const float* w, const float* logp, const int6
 /* p -= lr * (g*scale [+ wd*p] [momentum]); optionally zero g. world==1 fast path. */
 int dl_local_sgd(float* p, float* g, float* m, uint64_t n, float lr, float momentum,
                  float weight_decay, int nesterov, float grad_scale, int zero_grads, void* stream);
+/* Same update, reading the old parameters from p_in and writing the new ones to p (p_in may equal p). */
+int dl_local_sgd_from(float* p, const float* p_in, float* g, float* m, uint64_t n, float lr, float momentum,
+                      float weight_decay, int nesterov, float grad_scale, int zero_grads, void* stream);
 /* x -= alpha (x - c); c += world_scale * alpha (x_old - c)  (single-rank EA step) */
 int dl_local_ea(float* x, float* c, uint64_t n, float alpha, void* stream);
 /* Deterministic sum of (a[i]-b[i])^2 (b may be NULL) into out[0] (double).

@@ -57,3 +57,46 @@ def test_server_and_survivors_outlive_a_client_that_vanishes():
     total = server["center"].double() + dead["w"].double() + alive["w"].double()
     want = 100.0 + (100.0 + 2) + (100.0 + 8)
     torch.testing.assert_close(total, torch.full((40,), want, dtype=torch.float64), rtol=1e-5, atol=1e-4)
+
+
+def _w_dead_lock_holder(rank, world, job):
+    """Exclusive mode: rank 1 draws a ticket and dies with it; rank 2 must get the lock after one timeout."""
+    import ctypes as C
+    import time
+    import torch_distlearn_b200 as dl
+    from torch_distlearn_b200 import _lib
+    comm = dl.HostCommunicator(rank, world, name=job, heap_mb=4, timeout_s=1.0)
+    n = 64
+    center = comm.alloc(n, torch.float32, "center")
+    out = {}
+    if rank == 0:
+        center.tensor.fill_(10.0)
+    comm.barrier()
+    if rank == 1:
+        t = C.c_uint32()
+        _lib.check_host(_lib.host().dlh_debug_take_ticket(comm._h, 0, C.byref(t)))
+        out = {"ticket": int(t.value)}
+    comm.barrier()                      # the dead holder is in the queue before anybody else
+    if rank == 2:
+        x = torch.zeros(n)
+        t0 = time.time()
+        for _ in range(3):              # the first sync pays one timeout to skip the dead ticket, the others are immediate
+            comm.async_client_sync(0, x, center, n, 0.5, exclusive=True)
+        out = {"x": x.clone(), "seconds": time.time() - t0}
+    comm.barrier()
+    if rank == 0:
+        out = {"center": center.tensor.clone(), "syncs": comm.sync_count(0)}
+    comm.barrier()
+    comm.close()
+    return out
+
+
+@pytest.mark.timeout(120)
+def test_a_client_that_dies_holding_the_lock_does_not_block_the_others():
+    server, dead, alive = run_ranks(_w_dead_lock_holder, 3, timeout=90)
+    assert dead["ticket"] == 0
+    assert server["syncs"] == 3
+    assert 0.9 < alive["seconds"] < 20.0, alive["seconds"]      # one timeout (1 s), not three, and not forever
+    # three elastic moves with alpha = 0.5 from x = 0, c = 10:  (x, c) -> (5, 5) -> (5, 5) -> (5, 5)
+    torch.testing.assert_close(alive["x"], torch.full((64,), 5.0))
+    torch.testing.assert_close(server["center"], torch.full((64,), 5.0))

@@ -147,6 +147,8 @@ def cuda():
     _sig(lib, "dl_im2col5x5", i32, [vp, vp, i32, i32, i32, i32, C.c_longlong, vp])
     _sig(lib, "dl_col2im5x5", i32, [vp, vp, i32, i32, i32, i32, C.c_longlong, vp])
     _sig(lib, "dl_local_sgd", i32, [vp, vp, vp, u64, f32, f32, f32, i32, f32, i32, vp])
+    _sig(lib, "dl_local_sgd_from", i32, [vp, vp, vp, vp, u64, f32, f32, f32, i32, f32, i32, vp])
+    _sig(lib, "dl_async_ea_client_out", i32, [cp, i32, vp, vp, u64, u64, f32, i32, i32, vp])
     _sig(lib, "dl_local_ea", i32, [vp, vp, u64, f32, vp])
     _sig(lib, "dl_sumsq_scratch_bytes", sz, [])
     _sig(lib, "dl_sumsq_diff", i32, [vp, vp, u64, vp, vp, vp])
@@ -175,6 +177,7 @@ def host():
     _sig(lib, "dlh_fused_ea", i32, [vp, u64, u64, u64, u64, f32, i32, u32, i32, rp])
     _sig(lib, "dlh_broadcast", i32, [vp, u64, u64, u64, i32, u32, i32, rp])
     _sig(lib, "dlh_async_ea_client", i32, [vp, i32, vp, u64, u64, f32, i32])
+    _sig(lib, "dlh_debug_take_ticket", i32, [vp, i32, P(u32)])
     _sig(lib, "dlh_async_sync_count", i32, [vp, i32, P(u64)])
     _sig(lib, "dlh_mailbox_write", i32, [vp, i32, i32, u64])
     _sig(lib, "dlh_mailbox_read", i32, [vp, i32, i32, P(u64)])

@@ -15,13 +15,18 @@ def _stream(t: torch.Tensor) -> int:
 
 
 def local_sgd(p: torch.Tensor, g: torch.Tensor, m: Optional[torch.Tensor] = None, lr: float = 0.01, momentum: float = 0.0,
-              weight_decay: float = 0.0, nesterov: bool = False, grad_scale: float = 1.0, zero_grads: bool = False) -> None:
-    """p -= lr * (scale*g [+ wd*p] [momentum]) on flat fp32 CUDA vectors, in place; optional zero of g."""
+              weight_decay: float = 0.0, nesterov: bool = False, grad_scale: float = 1.0, zero_grads: bool = False,
+              p_in: Optional[torch.Tensor] = None) -> None:
+    """p = p_in - lr * (scale*g [+ wd*p_in] [momentum]) on flat fp32 CUDA vectors (p_in defaults to p: in place);
+    optional zero of g."""
     assert p.is_cuda and g.is_cuda and p.dtype == g.dtype == torch.float32 and p.is_contiguous() and g.is_contiguous()
     assert p.numel() == g.numel()
+    src = p if p_in is None else p_in
+    assert src.is_cuda and src.dtype == torch.float32 and src.is_contiguous() and src.numel() == p.numel()
     with torch.cuda.device(p.device):
-        _lib.check(_lib.cuda().dl_local_sgd(p.data_ptr(), g.data_ptr(), m.data_ptr() if m is not None else None, p.numel(), lr,
-                                            momentum, weight_decay, int(nesterov), grad_scale, int(zero_grads), _stream(p)))
+        _lib.check(_lib.cuda().dl_local_sgd_from(p.data_ptr(), src.data_ptr(), g.data_ptr(), m.data_ptr() if m is not None else None,
+                                                 p.numel(), lr, momentum, weight_decay, int(nesterov), grad_scale, int(zero_grads),
+                                                 _stream(p)))
 
 
 def local_ea(x: torch.Tensor, c: torch.Tensor, alpha: float) -> None:

@@ -528,11 +528,15 @@ class _CudaOps(Communicator):
         return self._mk_result(self._res)
 
     def async_client_sync(self, server: int, x: torch.Tensor, center: SymBuffer, n: int, alpha: float,
-                          exclusive: bool = False, nblocks: int = 0, stream=None):
+                          exclusive: bool = False, nblocks: int = 0, stream=None, x_out: Optional[torch.Tensor] = None):
+        """``x_out``: write the moved parameters there and leave ``x`` alone (so the sync can run under a forward /
+        backward pass that still reads ``x``)."""
         assert x.dtype == torch.float32 and x.is_contiguous() and x.is_cuda
+        out = x if x_out is None else x_out
+        assert out.dtype == torch.float32 and out.is_contiguous() and out.is_cuda and out.numel() >= n
         with torch.cuda.device(self.device):
-            _lib.check(self._lib.dl_async_ea_client(C.byref(self._c), server, x.data_ptr(), center.offset, n, alpha,
-                                                    int(exclusive), self._nb(nblocks), _stream_ptr(self.device, stream)))
+            _lib.check(self._lib.dl_async_ea_client_out(C.byref(self._c), server, x.data_ptr(), out.data_ptr(), center.offset, n,
+                                                        alpha, int(exclusive), self._nb(nblocks), _stream_ptr(self.device, stream)))
         self.launches += 1
 
     def peer_pull(self, src_rank: int, buf: SymBuffer, dst: torch.Tensor, n: Optional[int] = None, stream=None):

@@ -97,7 +97,8 @@ class FlatParams:
         cur = 0
         for s in self.sizes:
             self.offsets.append(cur)
-            cur += (s + 3) // 4 * 4  # keep every tensor 16-byte aligned inside the flat vector
+            cur += (s + 7) // 8 * 8  # every tensor starts on a 32-byte boundary: any range of whole tensors (a gradient
+            # bucket) can then go through the 256-bit paths of the collectives
         self.numel = cur
         self.padded = comm.padded(cur)
         self.params = comm.alloc(self.padded, torch.float32, name + ".params")
