@@ -59,7 +59,7 @@ class TrainStep:
             self.buckets.set_hyper(lr, momentum, weight_decay, nesterov)
 
     # ------------------------------------------------------------------------------------------------
-    def _body(self) -> None:
+    def _forward_backward(self) -> None:
         if self._fused_loss:
             out, loss = self.model.forward_with_loss(self.x, self.y)     # classifier head + loss in the model's own kernels
         else:
@@ -68,6 +68,9 @@ class TrainStep:
         loss.backward()
         self.logits = out.detach()
         self.loss.copy_(loss.detach())
+
+    def _body(self) -> None:
+        self._forward_backward()
         if self.buckets is not None:
             self.buckets.finish()           # the per-bucket kernels were launched from the backward hooks
         else:
@@ -130,14 +133,7 @@ class TrainStep:
         torch.cuda.synchronize(self.device)
         if not self.use_graph:
             return
-        self.graph = torch.cuda.CUDAGraph()
-        steps_before, launches_before, native_before = self.sgd.steps, self.sgd.comm.launches, self._native_count()
-        with torch.cuda.graph(self.graph):
-            self._body()
-        # the capture itself did not execute a step
-        self.sgd.steps, self.sgd.comm.launches = steps_before, launches_before
-        self._replayed_kernels -= self._native_count() - native_before
-        torch.cuda.synchronize(self.device)
+        self._recapture()              # the capture itself does not execute a step
 
     # ------------------------------------------------------------------------------------------------
     def load(self, x: torch.Tensor, y: torch.Tensor) -> None:
@@ -190,9 +186,172 @@ class TrainStep:
         return self.run()
 
     def loss_value(self) -> float:
-        """Device->host read of the last step's loss (synchronises)."""
+        """Device->host read of the last step's loss (synchronises).  Also the place where a collective that gave up
+        waiting for a peer surfaces: the sticky error word in pinned host memory is checked here (a plain load)."""
         if self.device.type == "cuda":
             self.loss_host.copy_(self.loss, non_blocking=True)
             torch.cuda.current_stream(self.device).synchronize()
+            poll = getattr(self.sgd.comm, "poll_error", None)
+            if poll is not None:
+                poll()
             return float(self.loss_host)
         return float(self.loss)
+
+    def set_lr(self, lr: float, momentum: Optional[float] = None, weight_decay: Optional[float] = None) -> None:
+        """Change the hyper-parameters of later steps (a learning-rate schedule).  They are kernel arguments, so a
+        captured graph has them baked in: the graph is dropped and captured again on the next ``run()`` (a few
+        milliseconds, no warm-up steps, training state untouched)."""
+        self.lr = float(lr)
+        if momentum is not None:
+            self.momentum = float(momentum)
+        if weight_decay is not None:
+            self.weight_decay = float(weight_decay)
+        if self.buckets is not None:
+            self.buckets.set_hyper(self.lr, self.momentum, self.weight_decay, self.nesterov)
+        if self.graph is not None:
+            self.graph = None
+            self._recapture()
+
+    def _recapture(self) -> None:
+        torch.cuda.synchronize(self.device)
+        graph = torch.cuda.CUDAGraph()
+        steps_before, launches_before, native_before = self.sgd.steps, self.sgd.comm.launches, self._native_count()
+        with torch.cuda.graph(graph):
+            self._body()
+        self.sgd.steps, self.sgd.comm.launches = steps_before, launches_before
+        self._replayed_kernels -= self._native_count() - native_before
+        torch.cuda.synchronize(self.device)
+        self.graph = graph
+
+
+class _LocalAlgo:
+    """What TrainStep needs from an algorithm object when the step itself does no collective."""
+
+    def __init__(self, comm):
+        self.comm = comm
+        self.steps = 0
+
+
+class EATrainStep(TrainStep):
+    """Elastic-averaging training on the flagship path: the reference's loop
+    ``df(params, x, y)`` -> local SGD -> ``averageParameters(params)`` (examples/client_remote.lua:192-210,
+    examples/mnist-ea.lua:100-110) with forward, backward and the local SGD kernel as ONE CUDA-graph replay per step,
+    and every ``tau``-th step one more launch: the fused elastic-average kernel (csrc/fused_ea.cu, lua/AllReduceEA.lua:34-45).
+    The center is double buffered, so the elastic kernel's arguments alternate and it stays outside the graph — one
+    asynchronous launch every ``tau`` steps.  Nodes may take different numbers of steps: ``ea.synchronizeCenter()`` /
+    ``ea.synchronizeParameters()`` drain as in the reference."""
+
+    def __init__(self, model: torch.nn.Module, flat: FlatParams, ea, batch_shape: Tuple[int, ...], lr: float,
+                 momentum: float = 0.0, weight_decay: float = 0.0, nesterov: bool = False, loss_fn: Optional[Callable] = None,
+                 use_graph: bool = True, target_dtype: torch.dtype = torch.int64, warmup: int = 3):
+        if momentum != 0.0 and flat.momentum is None:
+            raise ValueError("momentum needs FlatParams(with_momentum=True)")
+        super().__init__(model, flat, _LocalAlgo(ea.comm), batch_shape, lr, momentum, weight_decay, nesterov, loss_fn,
+                         use_graph, "auto", target_dtype, warmup)
+        self.ea = ea
+
+    def _local_sgd(self, p_in=None) -> None:
+        flat = self.flat
+        n = flat.padded
+        if self.device.type == "cuda":
+            from ..ops.local import local_sgd
+            local_sgd(flat.params.tensor[:n], flat.grads.tensor[:n], flat.momentum.tensor[:n] if self.momentum != 0.0 else None,
+                      lr=self.lr, momentum=self.momentum, weight_decay=self.weight_decay, nesterov=self.nesterov,
+                      zero_grads=True, p_in=p_in)
+            self.sgd.comm.launches += 1
+        else:
+            with torch.no_grad():
+                src = flat.params.tensor[:n] if p_in is None else p_in
+                g = flat.grads.tensor[:n]
+                if self.weight_decay:
+                    g = g + self.weight_decay * src
+                if self.momentum != 0.0:
+                    m = flat.momentum.tensor[:n]
+                    m.mul_(self.momentum).add_(g)
+                    g = g + self.momentum * m if self.nesterov else m
+                flat.params.tensor[:n].copy_(src - self.lr * g)
+                flat.grads.tensor[:n].zero_()
+
+    def _body(self) -> None:
+        self._forward_backward()
+        self._local_sgd()
+        self.sgd.steps += 1
+
+    def run(self) -> torch.Tensor:
+        loss = super().run()
+        self.ea.averageParameters(self.flat)      # counts the step; every tau-th call launches the fused elastic kernel
+        return loss
+
+
+class AsyncTrainStep(EATrainStep):
+    """The asynchronous EASGD client on the flagship path.  The reference's client does
+    ``grads at x`` -> ``syncClient`` (d = alpha (x - c); x -= d; c += d) -> ``x -= lr g`` (examples/EASGD_client.lua:106-117,
+    lua/AsyncEA.lua:134-146).  d depends only on x and the center, not on the gradient, so on a sync step the exchange
+    kernel (csrc/async_ea.cu) starts on a side stream at the SAME time as forward/backward, reads x, writes x - d into a
+    second buffer and adds d into the server's center over NVLink; when backward is done the SGD kernel forms
+    ``(x - d) - lr g``.  Same arithmetic and order of effects as the reference, with the exchange hidden under the compute.
+    Two graphs are captured: the plain step and the sync step."""
+
+    def __init__(self, model: torch.nn.Module, flat: FlatParams, client, batch_shape: Tuple[int, ...], lr: float, **kw):
+        if client.role != "client":
+            raise ValueError("AsyncTrainStep drives a client")
+        super().__init__(model, flat, client, batch_shape, lr, **kw)
+        self.client = client
+        self.graph_sync: Optional[torch.cuda.CUDAGraph] = None
+        self._moved = torch.empty_like(flat.params.tensor) if flat.device.type == "cuda" else None
+        self._side = torch.cuda.Stream(flat.device) if flat.device.type == "cuda" else None
+
+    def _sync_body(self) -> None:
+        cl, flat = self.client, self.flat
+        cur = torch.cuda.current_stream(self.device)
+        self._side.wait_stream(cur)
+        cl.comm.async_client_sync(cl.server_rank, flat.params.tensor, cl._center, cl._n, cl.alpha, cl.exclusive,
+                                  stream=self._side, x_out=self._moved)
+        self._forward_backward()
+        cur.wait_stream(self._side)
+        self._local_sgd(p_in=self._moved[:flat.padded])
+        self.sgd.steps += 1
+
+    def capture(self) -> None:
+        if self._captured:
+            return
+        if self.client._center is None:
+            raise RuntimeError("call client.initClient(flat) before the first step")
+        super().capture()
+        if self.graph is not None:
+            steps_before, launches_before, native_before = self.sgd.steps, self.sgd.comm.launches, self._native_count()
+            self.graph_sync = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(self.graph_sync):
+                self._sync_body()
+            self.sgd.steps, self.sgd.comm.launches = steps_before, launches_before
+            self._replayed_kernels -= self._native_count() - native_before
+            torch.cuda.synchronize(self.device)
+
+    def run(self) -> torch.Tensor:
+        if not self._captured:
+            self.capture()
+        cl = self.client
+        cl.step += 1
+        if cl.step % cl.tau != 0:
+            return TrainStep.run(self)
+        if self._staged:
+            cur = torch.cuda.current_stream(self.device)
+            cur.wait_event(self._staged_ev)
+            self.x.copy_(self._x_next, non_blocking=True)
+            self.y.copy_(self._y_next, non_blocking=True)
+            self._consumed_ev.record(cur)
+            self._staged = False
+        if self.graph_sync is not None:
+            self.graph_sync.replay()
+            self.sgd.steps += 1
+            self.sgd.comm.launches += self.launches_per_step + 1
+            self._replayed_kernels += self.kernels_per_step + 1
+        elif self.device.type == "cuda":
+            self._sync_body()
+        else:
+            self._forward_backward()
+            cl.step -= 1
+            cl.syncClient(self.flat)
+            self._local_sgd()
+            self.sgd.steps += 1
+        return self.loss
