@@ -10,6 +10,9 @@
 // Layout of the segment:  [header 4 KiB][heap of rank 0][heap of rank 1]...   and every heap
 // starts with a HostPad (DL_PAD_BYTES reserved, as on the GPU).
 #include <atomic>
+#include <map>
+#include <mutex>
+#include <string>
 #include <cerrno>
 #include <cstdarg>
 #include <cstdio>
@@ -176,7 +179,8 @@ int check(Handle* h, int ch) {
 // the update runs on the buffer, and the result is copied out to every rank.  Each loop is a plain a[i] op b[i] over
 // restrict pointers, which g++ vectorises; DLH_CLONES adds an AVX2 copy picked at load time.  Built with
 // -ffp-contract=off: no fused multiply-adds, the rounding is the one written here.
-#if defined(__x86_64__) && defined(__GNUC__) && !defined(__clang__)
+// (DLH_NO_CLONES: the sanitizer builds switch the ifunc-based dispatch off - its resolvers run before TSan is up)
+#if defined(__x86_64__) && defined(__GNUC__) && !defined(__clang__) && !defined(DLH_NO_CLONES)
 #define DLH_CLONES __attribute__((target_clones("avx2", "default")))
 #else
 #define DLH_CLONES
@@ -288,6 +292,47 @@ void reduce_typed<float>(Handle* h, uint64_t off, uint64_t n, uint32_t mask, boo
   stream_fence();
 }
 
+// Ranks that live in ONE process (threads, the way the reference's own tests run their nodes: ipc.map,
+// test/test_AllReduceSGD.lua:26-35) share a single mapping of the segment: one mmap per (process, segment), counted.
+// Besides saving address space this is what lets ThreadSanitizer see the cross-rank protocol at all — it tracks
+// accesses by virtual address, and two mappings of the same pages would hide every race from it.
+struct Mapping {
+  char* map;
+  size_t bytes;
+  int refs;
+};
+std::mutex g_maps_mu;
+std::map<std::string, Mapping> g_maps;
+
+char* acquire_existing(const char* name, size_t total) {
+  std::lock_guard<std::mutex> lk(g_maps_mu);
+  auto it = g_maps.find(name);
+  if (it == g_maps.end() || it->second.bytes != total) return nullptr;
+  ++it->second.refs;
+  return it->second.map;
+}
+// registers a fresh mapping, or - if another thread got there first - drops ours and returns theirs
+char* publish_mapping(const char* name, char* map, size_t total) {
+  std::lock_guard<std::mutex> lk(g_maps_mu);
+  auto it = g_maps.find(name);
+  if (it != g_maps.end() && it->second.bytes == total) {
+    munmap(map, total);
+    ++it->second.refs;
+    return it->second.map;
+  }
+  g_maps[name] = Mapping{map, total, 1};
+  return map;
+}
+void release_mapping(const char* name, char* map, size_t total) {
+  std::lock_guard<std::mutex> lk(g_maps_mu);
+  auto it = g_maps.find(name);
+  if (it != g_maps.end() && it->second.map == map) {
+    if (--it->second.refs > 0) return;
+    g_maps.erase(it);
+  }
+  munmap(map, total);
+}
+
 }  // namespace
 
 extern "C" {
@@ -302,6 +347,7 @@ int dlh_open(const char* name, int rank, int world, uint64_t heap_bytes, double 
   const size_t total = kHeaderBytes + static_cast<size_t>(world) * heap_bytes;
   const double limit = timeout_s > 0 ? timeout_s : 60.0;
   int fd = -1;
+  void* map = nullptr;
   if (rank == 0) {
     shm_unlink(name);
     fd = shm_open(name, O_CREAT | O_EXCL | O_RDWR, 0600);
@@ -313,6 +359,8 @@ int dlh_open(const char* name, int rank, int world, uint64_t heap_bytes, double 
   } else {
     const double t0 = now_s();
     while (true) {
+      map = acquire_existing(name, total);       // a rank of this very process has mapped the segment already
+      if (map) break;
       fd = shm_open(name, O_RDWR, 0600);
       if (fd >= 0) {
         struct stat st;
@@ -327,11 +375,14 @@ int dlh_open(const char* name, int rank, int world, uint64_t heap_bytes, double 
       usleep(1000);
     }
   }
-  void* map = mmap(nullptr, total, PROT_READ | PROT_WRITE, MAP_SHARED, fd, 0);
-  close(fd);
-  if (map == MAP_FAILED) {
-    set_error("mmap '%s': %s", name, strerror(errno));
-    return DL_ESYS;
+  if (!map) {
+    map = mmap(nullptr, total, PROT_READ | PROT_WRITE, MAP_SHARED, fd, 0);
+    close(fd);
+    if (map == MAP_FAILED) {
+      set_error("mmap '%s': %s", name, strerror(errno));
+      return DL_ESYS;
+    }
+    map = publish_mapping(name, static_cast<char*>(map), total);
   }
   Handle* h = new Handle();
   h->rank = rank;
@@ -353,7 +404,7 @@ int dlh_open(const char* name, int rank, int world, uint64_t heap_bytes, double 
     while (hdr->magic.load(std::memory_order_acquire) != kMagic) {
       if (now_s() - t0 > limit) {
         set_error("timed out waiting for rank 0 to initialise '%s'", name);
-        munmap(map, total);
+        release_mapping(name, static_cast<char*>(map), total);
         delete h;
         return DL_ETIMEOUT;
       }
@@ -361,7 +412,7 @@ int dlh_open(const char* name, int rank, int world, uint64_t heap_bytes, double 
     }
     if (hdr->world != static_cast<uint32_t>(world) || hdr->heap_bytes != heap_bytes) {
       set_error("segment '%s' was created with a different geometry", name);
-      munmap(map, total);
+      release_mapping(name, static_cast<char*>(map), total);
       delete h;
       return DL_EINVAL;
     }
@@ -374,7 +425,7 @@ int dlh_open(const char* name, int rank, int world, uint64_t heap_bytes, double 
       if (now_s() - t0 > limit) {
         set_error("timed out waiting for all %d ranks to attach to '%s'", world, name);
         if (rank == 0) shm_unlink(name);
-        munmap(map, total);
+        release_mapping(name, static_cast<char*>(map), total);
         delete h;
         return DL_ETIMEOUT;
       }
@@ -392,7 +443,7 @@ int dlh_close(void* handle, int unlink_name) {
   Handle* h = static_cast<Handle*>(handle);
   if (!h) return DL_OK;
   if (unlink_name) shm_unlink(h->name);
-  munmap(h->map, h->total_bytes);
+  release_mapping(h->name, h->map, h->total_bytes);
   delete h;
   return DL_OK;
 }
