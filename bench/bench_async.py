@@ -4,9 +4,12 @@
     python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29562 \
         bench/bench_async.py [--impl ours|hostloop] [--steps 200]
 
-ours     : rank 0 holds the center in its GPU's symmetric heap and does nothing per sync; every client
-           sync is ONE kernel on the client GPU (P2P loads of the center + red.add.v4.f32 of the elastic
-           difference over NVLink, csrc/async_ea.cu).
+ours     : the flagship path.  Rank 0 holds the center in its GPU's symmetric heap and does nothing per sync; clients
+           run AsyncTrainStep: tensor-core model, the step as a CUDA graph, and on every tau-th step the sync kernel
+           (P2P loads of the center + red.add.v4.f32 of the elastic difference over NVLink, csrc/async_ea.cu) on a side
+           stream UNDER forward/backward (parallel/trainer.py).
+ours_eager: the same transport driven the plain way: stock cuDNN model, eager loop, the sync kernel between backward
+           and the SGD update (round 1's arm).
 hostloop : the reference's design (lua/AsyncEA.lua:230-237; examples/AsyncEASGD.sh:36 runs the server
            without --cuda): a server process serialises the clients with recv-from-any, ships the center
            and receives the delta through host memory (torch.distributed gloo; NCCL has no any-source recv).
@@ -31,7 +34,7 @@ import torch.nn.functional as F
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--impl", choices=["ours", "hostloop"], default="ours")
+    ap.add_argument("--impl", choices=["ours", "ours_eager", "hostloop"], default="ours")
     ap.add_argument("--batch", type=int, default=128)
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--tau", type=int, default=10)
@@ -44,18 +47,23 @@ def main():
     dev = torch.device("cuda", local)
     torch.cuda.set_device(dev)
     dist.init_process_group("gloo", rank=rank, world_size=world)
-    from torch_distlearn_b200.models import cifar_convnet
+    # strict fp32 in every arm, like the headline bench (the reference casts everything to float, examples/cifar10.lua:136)
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    from torch_distlearn_b200.models import cifar_convnet, cifar_convnet_tc
     from torch_distlearn_b200.ops import local_sgd
-    model = cifar_convnet().to(dev)
+    model = (cifar_convnet_tc() if args.impl == "ours" else cifar_convnet()).to(dev)
     B, clients = args.batch, world - 1
     out = {}
-    if args.impl == "ours":
+    step = None
+    if args.impl in ("ours", "ours_eager"):
         import torch_distlearn_b200 as dl
-        comm = dl.P2PCommunicator(rank=rank, world=world, device=dev, heap_mb=96)
+        comm = dl.P2PCommunicator(rank=rank, world=world, device=dev, heap_mb=128)
         flat = dl.FlatParams(comm, model)
-        # tau = 1 inside the object: this script does the "every tau-th step" test itself so that both arms share it
-        algo = dl.AsyncEA(comm, "server" if rank == 0 else "client", 1, args.alpha, server_rank=0, num_clients=clients,
-                          exclusive=bool(args.exclusive))
+        # ours_eager: tau = 1 inside the object, this script does the "every tau-th step" test itself so that it shares
+        # the loop with the hostloop arm; ours: the object counts, AsyncTrainStep picks the plain or the sync graph
+        algo = dl.AsyncEA(comm, "server" if rank == 0 else "client", args.tau if args.impl == "ours" else 1, args.alpha,
+                          server_rank=0, num_clients=clients, exclusive=bool(args.exclusive))
         if rank == 0:
             algo.initServer(flat)
             t0 = time.time()
@@ -91,16 +99,26 @@ def main():
         g = torch.Generator().manual_seed(rank)
         x = torch.randn(B, 3, 32, 32, generator=g).to(dev)
         y = torch.randint(0, 10, (B,), generator=g).to(dev)
-        p = flat.params.tensor if args.impl == "ours" else flat.params
-        gr = flat.grads.tensor if args.impl == "ours" else flat.grads
+        p = flat.params.tensor if args.impl != "hostloop" else flat.params
+        gr = flat.grads.tensor if args.impl != "hostloop" else flat.grads
+        if args.impl == "ours":
+            from torch_distlearn_b200.parallel.trainer import AsyncTrainStep
+            step = AsyncTrainStep(model, flat, algo, (B, 3, 32, 32), lr=args.lr, use_graph=True)
+            step.load(x, y)
+            step.capture()
         sync_ms, n_sync = 0.0, 0
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
 
         def one_step(i, timed):
             nonlocal sync_ms, n_sync
+            if step is not None:
+                step.run()                                             # plain graph, or the graph with the sync under fwd/bwd
+                if algo.step % args.tau == 0 and timed:
+                    n_sync += 1
+                return
             F.nll_loss(model(x), y).backward()
             if (i + 1) % args.tau == 0:
-                if args.impl == "ours":
+                if args.impl == "ours_eager":
                     if timed:
                         ev0.record()
                     algo.syncClient(flat)
@@ -132,7 +150,7 @@ def main():
             one_step(i, True)
         torch.cuda.synchronize()
         wall = time.perf_counter() - t0
-        if args.impl == "ours":
+        if args.impl != "hostloop":
             algo.finish()
         else:
             req[0] = -1
@@ -145,6 +163,8 @@ def main():
         print(json.dumps({"bench": "async_easgd_cifar", "impl": args.impl, "n_gpus": world, "clients": clients, "per_gpu_batch": B,
                           "tau": args.tau, "alpha": args.alpha, "exclusive": bool(args.exclusive),
                           "client_samples_per_s_total": round(sum(c["samples_per_s"] for c in cl), 1),
+                          "client_samples_per_s_each": round(sum(c["samples_per_s"] for c in cl) / len(cl), 1),
+                          "sync_hidden_under_backward": args.impl == "ours",
                           "syncs_per_s": round(sum(c["syncs"] / c["wall_s"] for c in cl), 1),
                           "mean_sync_ms": round(sum(c["sync_ms"] for c in cl) / len(cl), 4),
                           "server_syncs_seen": res[0].get("syncs")}))

@@ -28,7 +28,16 @@ if ROOT not in sys.path:
 import torch
 import torch.distributed as dist
 
-LINK_GBS = 770.0  # measured peer copy bandwidth per direction per GPU (B200_PROFILING.md)
+LINK_GBS = 770.0  # per direction per GPU: the recipe's measured peer-copy figure (B200_PROFILING.md); replaced at run time by
+                  # the figure bench/peak.py measured in this repo (profiles/nvlink_peak.json) when that file is present
+
+
+def _measured_link_gbs():
+    path = os.path.join(ROOT, "profiles", "nvlink_peak.json")
+    try:
+        return float(json.load(open(path))["p2p_copy_gbs_per_direction"])
+    except Exception:  # noqa: BLE001 - no measurement yet: keep the recipe constant
+        return None
 
 
 GRAPH = False
@@ -77,9 +86,14 @@ def main():
     ap.add_argument("--nblocks", default="0", help="comma list of block counts to try for our kernels (0 = default)")
     ap.add_argument("--no-nccl", action="store_true")
     ap.add_argument("--graph", action="store_true", help="time CUDA-graph replays (no host launch cost in either arm)")
+    ap.add_argument("--permille", default="0,500,750,1000", help="switch shares tried for the hybrid variant (needs multicast)")
+    ap.add_argument("--variants", default="", help="comma list to restrict our variants (default: all that apply)")
     args = ap.parse_args()
-    global GRAPH
+    global GRAPH, LINK_GBS
     GRAPH = bool(args.graph)
+    link_source = "recipe constant (B200_PROFILING.md)"
+    if _measured_link_gbs():
+        LINK_GBS, link_source = _measured_link_gbs(), "profiles/nvlink_peak.json (bench/peak.py, this repo)"
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
     local = int(os.environ.get("LOCAL_RANK", rank))
     dev = torch.device("cuda", local)
@@ -101,7 +115,11 @@ def main():
     td = torch.zeros(max_n, device=dev)
     ops = args.ops.split(",")
     nblocks_list = [int(x) for x in args.nblocks.split(",")]
-    variants = ["oneshot", "twoshot"] + (["nvls"] if comm.has_multicast else [])
+    permilles = [int(x) for x in args.permille.split(",")] if comm.has_multicast else [0]
+    variants = ["ll", "oneshot", "twoshot"] + (["nvls"] if comm.has_multicast else []) + [f"hybrid{p}" for p in permilles]
+    if args.variants:
+        keep = set(args.variants.split(","))
+        variants = [v for v in variants if v in keep or (v.startswith("hybrid") and "hybrid" in keep)]
     rows = []
 
     def dev_sync():
@@ -123,9 +141,18 @@ def main():
         cur = [0]
         cands = {}
         for op in ops:
-            for v in variants:
+            for vname in variants:
+                v = vname
                 if v == "oneshot" and (nbytes > (2 << 20) or op == "fused_ea"):
                     continue
+                if v == "ll" and nbytes > comm.ll_max_bytes:
+                    continue
+                if v.startswith("hybrid"):
+                    if op == "broadcast" or nbytes < (64 << 10) or n % 8:
+                        continue
+                    pm = int(v[6:])
+                    comm._variants.hybrid_permille = {o: pm for o in comm._variants.OPS}
+                    v = "hybrid"
                 for nb in nblocks_list:
                     if op == "fused_sgd":
                         fn = lambda v=v, nb=nb: comm.fused_sgd(g, p, None, n, 1e-6, active=1, variant=v, zero_grads=False, nblocks=nb)
@@ -144,7 +171,7 @@ def main():
                         if rank == 0:
                             print(f"# {op} {v} {nbytes}: {e}", flush=True)
                         continue
-                    cands[(op, v, nb)] = us
+                    cands[(op, vname, nb)] = us
             if nccl is not None:
                 if op == "fused_sgd":
                     def fn():
@@ -164,9 +191,14 @@ def main():
                 algbw = nbytes / us / 1e3                       # GB/s
                 factor = 1.0 if op == "broadcast" else 2.0 * (world - 1) / world
                 if op == "broadcast":
-                    roof_bytes = nbytes * (1.0 if v != "twoshot" else (1.0 + 1.0 / world) * (world - 1) / world)
+                    roof_bytes = nbytes * 1.0        # every rank has to receive S, the root has to send S
                 elif v == "nvls":
                     roof_bytes = nbytes * (1.0 + 1.0 / world)
+                elif v.startswith("hybrid"):
+                    f = int(v[6:]) / 1000.0           # share through the switch: (1 + 1/N) S, the rest 2 (N-1)/N S
+                    roof_bytes = nbytes * (f * (1.0 + 1.0 / world) + (1.0 - f) * 2.0 * (world - 1) / world)
+                elif v == "ll":
+                    roof_bytes = nbytes * 2.0 * (world - 1)   # 2x packets, pushed to every peer
                 else:
                     roof_bytes = nbytes * 2.0 * (world - 1) / world
                 roof_us = roof_bytes / (LINK_GBS * 1e3)
@@ -178,7 +210,8 @@ def main():
     if rank == 0:
         if args.out:
             os.makedirs(os.path.dirname(os.path.abspath(args.out)), exist_ok=True)
-            json.dump({"world": world, "transport": comm.describe(), "link_gbs": LINK_GBS, "rows": rows}, open(args.out, "w"), indent=1)
+            json.dump({"world": world, "transport": comm.describe(), "link_gbs": LINK_GBS, "link_gbs_source": link_source,
+                       "rows": rows}, open(args.out, "w"), indent=1)
         if args.write_table:
             write_table(rows, world)
     dist.barrier()
@@ -186,26 +219,55 @@ def main():
 
 
 def write_table(rows, world):
-    """oneshot_max[op] = largest size at which one-shot is the fastest of our variants; nvls_min[op] =
-    smallest size from which NVLS beats two-shot at every larger size."""
+    """Turns a sweep into the size -> variant table that Communicator.pick_variant reads (parallel/variant_table.json):
+    ll_max[op]          largest size up to which the push path is the fastest of our variants at every smaller size too
+    oneshot_max[op]     same for the one-shot kernel (above ll_max)
+    hybrid_permille[op] switch share of the hybrid kernel that minimises the summed time over the sizes >= 4 MiB
+    hybrid_min[op]      smallest size from which that hybrid beats two-shot and NVLS at every larger size
+    nvls_min[op]        smallest size from which NVLS beats two-shot at every larger size (used below hybrid_min)."""
     ours = {}
     for r in rows:
         if r["impl"] == "nccl":
             continue
-        key = (r["op"], r["bytes"])
-        best = ours.setdefault(key, {})
+        best = ours.setdefault((r["op"], r["bytes"]), {})
         best[r["impl"]] = min(best.get(r["impl"], 1e30), r["us"])
-    table = {"world": world, "oneshot_max": {}, "nvls_min": {}}
-    for op in {k[0] for k in ours}:
+    table = {"world": world, "ll_max": {}, "oneshot_max": {}, "nvls_min": {}, "hybrid_min": {}, "hybrid_permille": {}}
+    for op in sorted({k[0] for k in ours}):
         sizes = sorted(b for (o, b) in ours if o == op)
+
+        def prefix_max(name):
+            top = 0
+            for b in sizes:
+                t = ours[(op, b)]
+                if name in t and t[name] <= min(t.values()) * 1.02:
+                    top = b
+                elif name in t or b > top:
+                    break
+            return top
+
+        table["ll_max"][op] = prefix_max("ll")
         one_max = 0
         for b in sizes:
-            t = ours[(op, b)]
-            if "oneshot" in t and t["oneshot"] <= min(v for k, v in t.items() if k != "oneshot"):
+            t = {k: v for k, v in ours[(op, b)].items() if k != "ll"}
+            if "oneshot" in t and t["oneshot"] <= min(t.values()):
                 one_max = b
-            else:
+            elif b > table["ll_max"][op]:
                 break
         table["oneshot_max"][op] = one_max
+        hybrids = sorted({k for b in sizes for k in ours[(op, b)] if k.startswith("hybrid")})
+        big = [b for b in sizes if b >= (4 << 20)]
+        if hybrids and big:
+            tot = {h: sum(ours[(op, b)].get(h, 1e30) for b in big) for h in hybrids}
+            h_best = min(tot, key=tot.get)
+            table["hybrid_permille"][op] = int(h_best[6:])
+            h_min = None
+            for b in reversed(sizes):
+                t = ours[(op, b)]
+                if h_best in t and t[h_best] <= min(t.get("twoshot", 1e30), t.get("nvls", 1e30)):
+                    h_min = b
+                else:
+                    break
+            table["hybrid_min"][op] = h_min if h_min is not None else 1 << 62
         nv_min = None
         for b in reversed(sizes):
             t = ours[(op, b)]
@@ -214,7 +276,7 @@ def write_table(rows, world):
             else:
                 break
         table["nvls_min"][op] = nv_min if nv_min is not None else 1 << 62
-    path = os.path.join(ROOT, "gpurun_out", f"variant_table_{world}.json")
+    path = os.path.join(ROOT, "gpurun_out", f"variant_table_{world}{'_graph' if GRAPH else ''}.json")
     json.dump(table, open(path, "w"), indent=1)
     print("# variant table ->", path, json.dumps(table))
 

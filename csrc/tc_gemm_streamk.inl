@@ -1,5 +1,6 @@
-// Stream-K ("persistent") form of the TS GEMM kernel — EXPERIMENTAL, off unless DL_B200_TC_STREAMK=1, and not yet run on
-// a GPU (written after the round's GPU budget was spent; tests/test_tc_gemm_gpu.py under that variable is the check).
+// Stream-K ("persistent") form of the TS GEMM kernel — the default since it was validated on a B200 (round 2:
+// tests/test_tc_streamk_gpu.py, 24 cases against the one-tile-per-CTA kernel and float64; flagship step 1.155 -> 1.132 ms,
+// profiles/bench_r2.md).  DL_B200_TC_STREAMK=0 or dl_tc_gemm_streamk(0) goes back to one tile per CTA.
 //
 // Why: one CTA per SM and 128 x BN tiles leave a tail.  The layer-2 forward GEMM has 256 tiles: 148 SMs run them as
 // two waves of 50 K-blocks, 100 K-block times for 86.5 K-block times of work (profiles/ncu_tc_gemm.md: "27 % second-
@@ -309,12 +310,12 @@ tc_gemm_sk_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
   }
 }
 
-// DL_B200_TC_STREAMK=1 selects this kernel (needs the TS layout, i.e. DL_B200_TC_TS unset or 1)
+// On by default; DL_B200_TC_STREAMK=0 deselects this kernel (it needs the TS layout, i.e. DL_B200_TC_TS unset or 1)
 int g_streamk = -1;   // -1: not decided yet (environment), 0 / 1: off / on (dl_tc_gemm_streamk)
 bool use_streamk() {
   if (g_streamk < 0) {
     const char* e = getenv("DL_B200_TC_STREAMK");
-    g_streamk = (e != nullptr && e[0] == '1') ? 1 : 0;
+    g_streamk = (e != nullptr && e[0] == '0') ? 0 : 1;   // on unless DL_B200_TC_STREAMK=0
   }
   return g_streamk != 0;
 }

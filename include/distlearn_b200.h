@@ -168,6 +168,13 @@ int dl_broadcast(const dl_comm_t* c, uint64_t off, uint64_t off2, uint64_t n, in
 int dl_host_words_alloc(void** host_ptr, void** dev_ptr);
 int dl_host_words_free(void* host_ptr);
 
+/* Bandwidth probes behind the roofline denominators (csrc/peak.cu, bench/peak.py; no counterpart in the reference, which
+ * publishes no numbers): stream n floats between the local heap and `peer`'s (mode 0 pull, 1 push) or through the
+ * multicast mapping (mode 2 multimem.st, 3 multimem.ld_reduce); dl_peak_memcpy is the same transfer on the copy engine. */
+int dl_peak_stream(const dl_comm_t* c, int mode, int peer, uint64_t src_off, uint64_t dst_off, uint64_t n, int nblocks,
+                   void* stream);
+int dl_peak_memcpy(const dl_comm_t* c, int peer, int pull, uint64_t src_off, uint64_t dst_off, uint64_t bytes, void* stream);
+
 /* Memory-model litmus tests of the signalling patterns on the real fabric (csrc/litmus.cu; the reference has no
  * counterpart - it synchronises with blocking sockets).  shape 0 = message passing around the ring of ranks (data
  * stores, release fence, flag | poll, acquire fence, data loads), shape 1 = store buffering with fence.sc.sys;
@@ -239,10 +246,10 @@ int dl_tc_gemm_ex(const float* A, const float* B, float* C, const float* bias, i
 int dl_tc_conv5x5(int mode, const float* act, const float* w, float* out, const float* bias, int B, int H, int W,
                   int Cin, int Cout, int split_k, int accumulate, int terms, void* stream);
 
-/* EXPERIMENTAL (not yet validated on a GPU): stream-K form of the tensor-core GEMM — one persistent CTA per SM takes a
- * contiguous range of (tile, K-block) units, so 256 tiles on 148 SMs cost 86.5 K-block times instead of 100
- * (csrc/tc_gemm_streamk.inl).  on = 1 / 0 switches it for later dl_tc_gemm* / dl_tc_conv5x5 calls (initial value:
- * environment variable DL_B200_TC_STREAMK, default 0); returns the previous setting. */
+/* Stream-K form of the tensor-core GEMM — one persistent CTA per SM takes a contiguous range of (tile, K-block) units,
+ * so 256 tiles on 148 SMs cost 86.5 K-block times instead of 100 (csrc/tc_gemm_streamk.inl).  on = 1 / 0 switches it
+ * for later dl_tc_gemm* / dl_tc_conv5x5 calls (initial value: 1 unless the environment says DL_B200_TC_STREAMK=0);
+ * returns the previous setting. */
 int dl_tc_gemm_streamk(int on);
 /* Host-side view of the stream-K decomposition (same code as the kernel): the segments (m0, n0, first K block, K blocks)
  * of CTA `cta`; returns their number, *grid = CTAs the launch would use on `sms` SMs. */

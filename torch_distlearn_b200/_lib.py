@@ -112,6 +112,8 @@ def cuda():
     _sig(lib, "dl_enable_peer", i32, [i32, i32])
     _sig(lib, "dl_can_access_peer", i32, [i32, i32, P(i32)])
     _sig(lib, "dl_memset_sync", i32, [i32, vp, i32, sz])
+    _sig(lib, "dl_peak_stream", i32, [cp, i32, i32, u64, u64, u64, i32, vp])
+    _sig(lib, "dl_peak_memcpy", i32, [cp, i32, i32, u64, u64, u64, vp])
     _sig(lib, "dl_litmus_scratch_bytes", sz, [i32, i32])
     _sig(lib, "dl_litmus", i32, [cp, i32, i32, u64, i32, u32, i32, vp])
     _sig(lib, "dl_host_words_alloc", i32, [P(vp), P(vp)])

@@ -35,6 +35,7 @@ CUDA_SOURCES = [
     "local_ops.cu",
     "ll_ops.cu",
     "litmus.cu",
+    "peak.cu",
     "tc_gemm.cu",
     "conv_ops.cu",
     "bn_ops.cu",
