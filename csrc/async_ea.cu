@@ -190,6 +190,20 @@ extern "C" int dl_async_sync_count(const dl_comm_t* c, int server, uint64_t* cou
   return DL_OK;
 }
 
+// Everything a polling host wants from rank `rank`'s control block in ONE copy: out[0] = sync counter, out[1..32] = the
+// mailbox words.  (The server's wait loop used to issue one blocking copy per word, up to nine per tick.)
+extern "C" int dl_async_ctl_snapshot(const dl_comm_t* c, int rank, uint64_t* out, void* stream) {
+  int nb = dl_check_comm(c, 0, 1);
+  if (nb < 0) return nb;
+  DL_REQUIRE(rank >= 0 && rank < c->world && out, "dl_async_ctl_snapshot: bad arguments");
+  static_assert(offsetof(DlAsyncCtl, mailbox) == offsetof(DlAsyncCtl, sync_count) + sizeof(unsigned long long), "layout");
+  const DlAsyncCtl* ctl = reinterpret_cast<const DlAsyncCtl*>(reinterpret_cast<const char*>(c->base[rank]) + DL_ASYNC_CTL_OFFSET);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  DL_CUDA(cudaMemcpyAsync(out, &ctl->sync_count, (1 + DL_MAILBOX_WORDS) * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+  DL_CUDA(cudaStreamSynchronize(st));
+  return DL_OK;
+}
+
 // ---- host-visible mailbox words in a rank's pad (tester handshake, ready/done flags) ----------
 extern "C" int dl_mailbox_write(const dl_comm_t* c, int rank, int index, uint64_t value, void* stream) {
   int nb = dl_check_comm(c, 0, 1);

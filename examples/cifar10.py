@@ -75,8 +75,11 @@ def main(argv=None):
                 loss_sum += float(loss)
             thr.add(b.batchSize)
             log.progress(i, n_train)
-        cm.allReduce()                                              # :203
+        # The drain first, the metrics after (the reference has them the other way round, :203 then :208): a node whose
+        # partition had fewer batches must be able to serve its peers' remaining steps from synchronizeParameters; were
+        # it parked in the confusion-matrix collective instead, nobody could make progress until the timeout.
         winner = sgd.synchronizeParameters()                        # :208
+        cm.allReduce()                                              # :203
         comm.synchronize()
         log.print(f"epoch {epoch} train: accuracy {100 * cm.totalValid:.2f}%  {thr.rate() * comm.world:.0f} samples/s (all nodes)"
                   f"  params from node {winner + 1}")

@@ -5,10 +5,10 @@
 cd "$(dirname "$0")"
 host=${HOST:-127.0.0.1}
 port=${PORT:-8080}
-OMP_NUM_THREADS=4 python client_remote.py --numNodes 2 --nodeIndex 1 --host $host --port $port "$@" &
+OMP_NUM_THREADS=4 python client_remote.py --backend dist --numNodes 2 --nodeIndex 1 --host $host --port $port "$@" &
 if python -c "import torch,sys; sys.exit(0 if torch.cuda.is_available() else 1)"; then
-  python client_remote.py --numNodes 2 --nodeIndex 2 --host $host --port $port --cuda --gpu 1 "$@" &
+  python client_remote.py --backend dist --numNodes 2 --nodeIndex 2 --host $host --port $port --cuda --gpu 1 "$@" &
 else
-  OMP_NUM_THREADS=4 python client_remote.py --numNodes 2 --nodeIndex 2 --host $host --port $port "$@" &
+  OMP_NUM_THREADS=4 python client_remote.py --backend dist --numNodes 2 --nodeIndex 2 --host $host --port $port "$@" &
 fi
 wait

@@ -215,6 +215,9 @@ int dl_peer_pull(const dl_comm_t* c, int src_rank, uint64_t off, float* dst, uin
 /* Read the server's sync counter (number of completed client syncs). */
 int dl_async_sync_count(const dl_comm_t* c, int server, uint64_t* count, void* stream);
 
+/* Sync counter (out[0]) and all 32 mailbox words (out[1..32]) of rank `rank` in one copy: what a server or tester
+ * polls while it waits (lua/AsyncEA.lua:163-177 blocks in recvAny instead). */
+int dl_async_ctl_snapshot(const dl_comm_t* c, int rank, uint64_t* out, void* stream);
 /* Host-visible 64-bit mailbox words in rank `rank`'s pad (index < 32): the tester handshake
  * "Test?"/"Ack" (lua/AsyncEA.lua:239-258,268-292) and ready/done flags travel here. */
 int dl_mailbox_write(const dl_comm_t* c, int rank, int index, uint64_t value, void* stream);

@@ -65,7 +65,7 @@ def _w_dead_lock_holder(rank, world, job):
     import time
     import torch_distlearn_b200 as dl
     from torch_distlearn_b200 import _lib
-    comm = dl.HostCommunicator(rank, world, name=job, heap_mb=4, timeout_s=1.0)
+    comm = dl.HostCommunicator(rank, world, name=job, heap_mb=4, timeout_s=30.0)
     n = 64
     center = comm.alloc(n, torch.float32, "center")
     out = {}
@@ -79,10 +79,12 @@ def _w_dead_lock_holder(rank, world, job):
     comm.barrier()                      # the dead holder is in the queue before anybody else
     if rank == 2:
         x = torch.zeros(n)
+        comm.set_timeout(1.0)           # the lock's patience; the barriers of the others keep their 30 s
         t0 = time.time()
         for _ in range(3):              # the first sync pays one timeout to skip the dead ticket, the others are immediate
             comm.async_client_sync(0, x, center, n, 0.5, exclusive=True)
         out = {"x": x.clone(), "seconds": time.time() - t0}
+        comm.set_timeout(30.0)
     comm.barrier()
     if rank == 0:
         out = {"center": center.tensor.clone(), "syncs": comm.sync_count(0)}
@@ -100,3 +102,59 @@ def test_a_client_that_dies_holding_the_lock_does_not_block_the_others():
     # three elastic moves with alpha = 0.5 from x = 0, c = 10:  (x, c) -> (5, 5) -> (5, 5) -> (5, 5)
     torch.testing.assert_close(alive["x"], torch.full((64,), 5.0))
     torch.testing.assert_close(server["center"], torch.full((64,), 5.0))
+
+
+def _w_torn_snapshot(rank, world, job):
+    """Rank 0 holds the center, ranks 1-2 keep adding POSITIVE elastic differences to it (x far above c), rank 3 pulls
+    copies of the center while they do.  Every element of the center only ever grows, so 'bounded by before and after'
+    is checkable element by element."""
+    import time
+    import torch_distlearn_b200 as dl
+    comm = dl.HostCommunicator(rank, world, name=job, heap_mb=4, timeout_s=30)
+    n = 4096
+    center = comm.alloc(n, torch.float32, "center")
+    if rank == 0:
+        center.tensor.zero_()
+    comm.barrier()
+    out = {}
+    if rank in (1, 2):
+        x = torch.full((n,), 1000.0)
+        for _ in range(300):
+            comm.async_client_sync(0, x, center, n, 0.01, exclusive=False)
+            x.fill_(1000.0)
+        out = {"syncs": 300}
+    elif rank == 3:
+        copies, dst = [], torch.zeros(n)
+        t0 = time.time()
+        while comm.sync_count(0) < 600 and time.time() - t0 < 60:
+            before = comm.sync_count(0)
+            comm.peer_pull(0, center, dst, n)
+            after = comm.sync_count(0)
+            copies.append((before, dst.clone(), after))
+        out = {"copies": copies[:: max(1, len(copies) // 50)]}
+    comm.barrier()
+    if rank == 0:
+        out = {"final": center.tensor.clone(), "syncs": comm.sync_count(0)}
+    comm.barrier()
+    comm.close()
+    return out
+
+
+@pytest.mark.timeout(180)
+def test_tester_snapshot_under_traffic_is_torn_but_bounded():
+    """docs/AsyncEA.md "What a reader of the center sees": a pull taken during lock-free traffic is not a consistent cut,
+    but every element lies between the center before and after the pull window."""
+    server, _, _, tester = run_ranks(_w_torn_snapshot, 4, timeout=150)
+    assert server["syncs"] == 600
+    final = server["final"]
+    assert tester["copies"], "the tester must have managed at least one pull during the traffic"
+    torn = 0
+    prev = torch.zeros_like(final)
+    for before, copy, after in tester["copies"]:
+        assert torch.all(copy >= prev - 1e-3), "the center only grows in this scenario: a later copy cannot be below an earlier one"
+        assert torch.all(copy <= final + 1e-3), "no element can exceed the final center"
+        if before != after and float(copy.max() - copy.min()) > 0:
+            torn += 1                      # elements from different moments: the documented tear
+        prev = copy
+    # (whether a tear is caught depends on timing; what must hold is the bound above)
+    assert torn >= 0

@@ -133,6 +133,7 @@ def cuda():
     _sig(lib, "dl_async_ea_client", i32, [cp, i32, vp, u64, u64, f32, i32, i32, vp])
     _sig(lib, "dl_peer_pull", i32, [cp, i32, u64, vp, u64, i32, vp])
     _sig(lib, "dl_async_sync_count", i32, [cp, i32, P(u64), vp])
+    _sig(lib, "dl_async_ctl_snapshot", i32, [cp, i32, P(u64), vp])
     _sig(lib, "dl_mailbox_write", i32, [cp, i32, i32, u64, vp])
     _sig(lib, "dl_mailbox_read", i32, [cp, i32, i32, P(u64), vp])
     _sig(lib, "dl_tc_gemm", i32, [vp, vp, vp, vp, i32, i32, i32, C.c_longlong, C.c_longlong, C.c_longlong, i32, i32, i32, vp])

@@ -129,23 +129,30 @@ class AsyncEA:
         (lua/AsyncEA.lua:230-237, :222-226).  Returns False when every client has finished."""
         self._log("Server waiting to sync")
 
+        last = {}
+
         def ready():
-            return self.comm.sync_count(self.server_rank) > self._seen_syncs or self._all_clients_done()
+            # one snapshot per tick: the sync counter and every client's "done" word arrive in a single small copy
+            count, words = self.comm.ctl_snapshot(self.server_rank)
+            last["count"], last["done"] = count, self._count_done(words)
+            return count > self._seen_syncs or last["done"]
 
         self._wait(ready, timeout, "a client sync")
-        count = self.comm.sync_count(self.server_rank)
-        if count == self._seen_syncs and self._all_clients_done():
+        count = last["count"]
+        if count == self._seen_syncs and last["done"]:
             return False
         self._seen_syncs = count
         self._x[:self._n].copy_(self._center.tensor[:self._n])
         self._unpack()
         return True
 
-    def _all_clients_done(self) -> bool:
+    def _count_done(self, words) -> bool:
         if self.num_clients is None:
             return False
-        done = sum(1 for r in range(self.comm.world) if self.comm.mailbox_read(self.server_rank, MB_DONE_BASE + r) == 1)
-        return done >= self.num_clients
+        return sum(1 for r in range(self.comm.world) if words[MB_DONE_BASE + r] == 1) >= self.num_clients
+
+    def _all_clients_done(self) -> bool:
+        return self._count_done(self.comm.ctl_snapshot(self.server_rank)[1])
 
     @property
     def syncs(self) -> int:
@@ -177,8 +184,8 @@ class AsyncEA:
         self.comm.mailbox_write(self.server_rank, MB_PULLED_BASE + self.comm.rank, 1)
         if self.num_clients is not None:
             def all_pulled():
-                return sum(1 for r in range(self.comm.world)
-                           if self.comm.mailbox_read(self.server_rank, MB_PULLED_BASE + r) == 1) >= self.num_clients
+                words = self.comm.ctl_snapshot(self.server_rank)[1]
+                return sum(1 for r in range(self.comm.world) if words[MB_PULLED_BASE + r] == 1) >= self.num_clients
             self._wait(all_pulled, timeout, "every client to pull the initial center")
 
     def syncClient(self, params: Any = None) -> bool:
@@ -205,12 +212,15 @@ class AsyncEA:
     def startTest(self, params: Any = None, timeout: Optional[float] = None) -> bool:
         """Wait for a test request, then params <- center (lua/AsyncEA.lua:268-285).  Returns False if
         the server said stop."""
+        last = {}
+
         def cond():
-            return self.comm.mailbox_read(self.server_rank, MB_TEST_SEQ) > self._seen_tests or \
-                self.comm.mailbox_read(self.server_rank, MB_STOP) == 1
+            words = self.comm.ctl_snapshot(self.server_rank)[1]
+            last["seq"] = words[MB_TEST_SEQ]
+            return words[MB_TEST_SEQ] > self._seen_tests or words[MB_STOP] == 1
 
         self._wait(cond, timeout, "a test request")
-        seq = self.comm.mailbox_read(self.server_rank, MB_TEST_SEQ)
+        seq = last["seq"]
         if seq == self._seen_tests:
             return False
         self._seen_tests = seq

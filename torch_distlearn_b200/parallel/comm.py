@@ -233,6 +233,11 @@ class Communicator:
     has_multicast = False
     ll_max_bytes = 0            # largest message the small-message staging area can take (0: none)
 
+    def ctl_snapshot(self, rank: int):
+        """(sync counter, the 32 mailbox words) of ``rank``'s async-EASGD control block.  Backends that can fetch them
+        in one go override this; the default asks word by word."""
+        return self.sync_count(rank), [self.mailbox_read(rank, i) for i in range(32)]
+
     def close(self) -> None:
         pass
 
@@ -552,6 +557,15 @@ class _CudaOps(Communicator):
         with torch.cuda.device(self.device):
             _lib.check(self._lib.dl_async_sync_count(C.byref(self._c), server, C.byref(v), _stream_ptr(self.device)))
         return int(v.value)
+
+    def ctl_snapshot(self, rank: int):
+        """One small device-to-host copy on a private stream (never queued behind the training stream's kernels)."""
+        if self.__dict__.get("_poll_stream") is None:
+            self._poll_stream = torch.cuda.Stream(self.device)
+            self._poll_buf = (C.c_uint64 * 33)()
+        with torch.cuda.device(self.device):
+            _lib.check(self._lib.dl_async_ctl_snapshot(C.byref(self._c), rank, self._poll_buf, self._poll_stream.cuda_stream))
+        return int(self._poll_buf[0]), [int(self._poll_buf[1 + i]) for i in range(32)]
 
     def mailbox_write(self, rank: int, index: int, value: int) -> None:
         with torch.cuda.device(self.device):
