@@ -4,8 +4,10 @@
     python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29561 \
         bench/bench_ea.py [--impl ours|nccl] [--batch 1] [--steps 2000]
 
-Every rank runs local SGD steps (forward + backward + local update captured in one CUDA graph in both
-arms, so the comparison isolates the elastic-averaging exchange); every tau-th step runs the exchange:
+ours: the local step (forward + backward + SGD) is ONE kernel (csrc/mnist_step.cu: an 8-CTA cluster, batch <= 8) and
+every tau-th step adds ONE more, the fused elastic average (the LL push variant at this size).  `--fused 0` and the nccl
+arm run the stock torch model instead, with forward + backward + local update captured in one CUDA graph (~25 small
+library kernels), which is what round 1 measured in both arms.  Every tau-th step runs the exchange:
 ours = ONE fused kernel (csrc/fused_ea.cu), nccl = 3 elementwise kernels + all_reduce + 1 elementwise
 kernel (lua/AllReduceEA.lua:34-45 spelled with torch ops).  Time: CUDA events around all steps, max
 over ranks.  Prints one JSON line on rank 0."""
@@ -33,6 +35,7 @@ def main():
     ap.add_argument("--tau", type=int, default=10)
     ap.add_argument("--alpha", type=float, default=0.2)
     ap.add_argument("--lr", type=float, default=0.01)
+    ap.add_argument("--fused", type=int, default=1, help="ours: the one-kernel MNIST step (batch <= 8)")
     args = ap.parse_args()
     rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
     local = int(os.environ.get("LOCAL_RANK", rank))
@@ -68,7 +71,16 @@ def main():
         p, gr = flat.params, flat.grads
         exchange = ea.average_parameters
 
+    fused = args.impl == "ours" and args.fused and B <= 8
+    if fused:
+        from torch_distlearn_b200.ops.mnist import mnist_step, model_tensors
+        mp, mg = model_tensors(model)
+        loss_dev = torch.zeros(1, device=dev)
+
     def local_step():
+        if fused:
+            mnist_step(x, y, mp, mg, loss_dev, None, lr=args.lr, apply_sgd=True)       # examples/mnist-ea.lua:100-107 in one launch
+            return
         F.nll_loss(model(x), y).backward()
         local_sgd(p, gr, None, lr=args.lr, zero_grads=True)
 
@@ -102,7 +114,8 @@ def main():
     torch.cuda.synchronize()
     ms = max_over_ranks(e0.elapsed_time(e1), world)
     if rank == 0:
-        print(json.dumps({"bench": "mnist_allreduce_ea", "impl": args.impl, "n_gpus": world, "per_gpu_batch": B, "tau": args.tau,
+        print(json.dumps({"bench": "mnist_allreduce_ea", "impl": args.impl, "fused_local_step": bool(fused), "n_gpus": world,
+                          "per_gpu_batch": B, "tau": args.tau,
                           "alpha": args.alpha, "steps": args.steps, "ms_per_step": round(ms / args.steps, 5),
                           "samples_per_s": round(B * world * args.steps / (ms / 1e3), 1),
                           "exchanges_per_s": round(args.steps / args.tau / (ms / 1e3), 1)}))

@@ -1,0 +1,391 @@
+// One training step of the reference's MNIST network as ONE kernel — SURVEY C6/C7, §2.7.
+//
+// The model of examples/mnist.lua:53-81 is tiny (10,842 parameters, 2.5 MFLOP per sample) and the reference trains
+// it at batch size 1 (:33): forward + backward + SGD is ~25 library kernels of a few microseconds each, 95 us per step
+// even inside a CUDA graph, and that is what every MNIST configuration really measures.  Here the whole step
+//
+//     Reshape(1,32,32) -> conv 1->16 5x5 -> tanh -> maxpool 2 -> conv 16->16 5x5 -> tanh -> maxpool 2
+//     -> Linear 400->10 -> logSoftMax -> NLL,  its backward pass,  and  p -= lr * g            (:53-66, :79, :86, :112-116)
+//
+// runs in one launch of a thread-block CLUSTER of 8 CTAs.  CTA r owns feature channels 2r and 2r+1 of both convolution
+// layers end to end — their filters, activations, gradients and the matching 50 columns of the Linear layer live in
+// its shared memory — and the three places where channels meet go through distributed shared memory:
+//   * after conv1 every CTA writes its two pooled maps into the shared memory of all eight (all-gather);
+//   * the Linear layer's ten partial sums of each CTA are written to all eight and added in rank order (all-reduce);
+//   * conv2's input gradient: CTA r forms the contribution of ITS two output channels to all 16 input channels and
+//     writes channel pair j's part into CTA j's slot r; CTA j adds its eight slots in rank order (reduce-scatter).
+// Three cluster barriers per sample, no global memory traffic besides the 4 KB input and (once per launch) the
+// parameters.  Every sum has a fixed order: two runs give the same bits.
+//
+// Batches: the cluster walks its samples one after another and accumulates the gradients in shared memory; with more
+// than one cluster (B > 8 or so) each takes every n-th sample and the gradients meet in global memory with atomics, the
+// update then being a separate dl_local_sgd.  With ONE cluster and apply_sgd != 0 the update is fused: one launch per step.
+#include <cooperative_groups.h>
+
+#include "dl_common.cuh"
+#include "dl_host.h"
+
+namespace cg = cooperative_groups;
+
+#define MN_CL 8      // CTAs per cluster: 2 of the 16 channels each
+#define MN_T 320     // threads per CTA = 2 output channels x 10 output rows x 16 input channels (conv2's natural shape)
+
+struct MnistArgs {
+  const float* x;            // [B, 1024]
+  const long long* y;        // [B]
+  float* p[6];               // conv1.weight [16,1,5,5], conv1.bias [16], conv2.weight [16,16,5,5], conv2.bias [16],
+  float* g[6];               //   linear.weight [10,400], linear.bias [10]  — and their gradients (may alias a flat vector)
+  float* loss;               // mean NLL of the batch
+  float* logp;               // [B, 10] or NULL
+  int B;
+  float lr;
+  int apply_sgd;             // 1: p -= lr * g inside the kernel (single cluster only); 0: g += gradient
+};
+
+struct MnistSmem {
+  float x[1024];
+  float w1[2][25], b1[2];
+  float a1[2][28 * 28];        // tanh(conv1); overwritten by the gradient w.r.t. conv1's pre-activation in the backward pass
+  unsigned char i1[2][196];    // arg-max position (0..3) inside each pooling window
+  float p1[16][196];           // pooled conv1 maps of ALL channels (gathered through DSMEM)
+  float w2[2][16][25], b2[2];
+  float a2[2][100];            // tanh(conv2), later its pre-activation gradient
+  unsigned char i2[2][25];
+  float p2[2][25];             // this CTA's 50 features
+  float w3[10][50], b3[10];
+  float lpart[MN_CL][10];      // partial logits of every CTA (all-reduce slots)
+  float dl[10];                // dlogits
+  float dfeat[2][25];
+  float dpart[MN_CL][2][196];  // conv2 dgrad contributions for MY two channels, one slot per source CTA
+  float gw1[2][25], gb1[2], gw2[2][16][25], gb2[2], gw3[10][50], gb3[10];   // gradient accumulators over the batch
+  float loss_acc;
+};
+
+__device__ __forceinline__ float warp_sum16(float v) {  // sum over the 16 lanes of a half warp (lanes differing in bits 0..3)
+  v += __shfl_xor_sync(0xffffffffu, v, 8);
+  v += __shfl_xor_sync(0xffffffffu, v, 4);
+  v += __shfl_xor_sync(0xffffffffu, v, 2);
+  v += __shfl_xor_sync(0xffffffffu, v, 1);
+  return v;
+}
+
+__global__ void __cluster_dims__(MN_CL, 1, 1) __launch_bounds__(MN_T, 1) mnist_step_kernel(MnistArgs a) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  MnistSmem& s = *reinterpret_cast<MnistSmem*>(smem_raw);
+  cg::cluster_group cluster = cg::this_cluster();
+  const int r = static_cast<int>(cluster.block_rank());          // owns channels 2r, 2r+1
+  const int cid = static_cast<int>(blockIdx.x) / MN_CL;           // which cluster
+  const int ncl = static_cast<int>(gridDim.x) / MN_CL;
+  const int t = threadIdx.x;
+  MnistSmem* peer[MN_CL];
+#pragma unroll
+  for (int k = 0; k < MN_CL; ++k) peer[k] = cluster.map_shared_rank(&s, k);
+
+  // ---- parameters of my channels into shared memory, gradient accumulators to zero ---------------------------
+  for (int i = t; i < 50; i += MN_T) (&s.w1[0][0])[i] = a.p[0][(2 * r) * 25 + i];
+  for (int i = t; i < 800; i += MN_T) (&s.w2[0][0][0])[i] = a.p[2][(2 * r) * 400 + i];
+  for (int i = t; i < 500; i += MN_T) {
+    const int j = i / 50, f = i - j * 50;
+    s.w3[j][f] = a.p[4][j * 400 + 2 * r * 25 + f];
+  }
+  if (t < 2) { s.b1[t] = a.p[1][2 * r + t]; s.b2[t] = a.p[3][2 * r + t]; }
+  if (t < 10) s.b3[t] = a.p[5][t];
+  for (int i = t; i < 50; i += MN_T) (&s.gw1[0][0])[i] = 0.f;
+  for (int i = t; i < 800; i += MN_T) (&s.gw2[0][0][0])[i] = 0.f;
+  for (int i = t; i < 500; i += MN_T) (&s.gw3[0][0])[i] = 0.f;
+  if (t < 2) { s.gb1[t] = 0.f; s.gb2[t] = 0.f; }
+  if (t < 10) s.gb3[t] = 0.f;
+  if (t == 0) s.loss_acc = 0.f;
+  const float inv_b = 1.f / static_cast<float>(a.B);
+  cluster.sync();   // everybody's shared memory exists and is initialised before anyone writes into it remotely
+
+  for (int b = cid; b < a.B; b += ncl) {
+    // ---- input -------------------------------------------------------------------------------------------------
+    const float4* xin = reinterpret_cast<const float4*>(a.x + static_cast<long long>(b) * 1024);
+    for (int i = t; i < 256; i += MN_T) reinterpret_cast<float4*>(s.x)[i] = xin[i];
+    __syncthreads();
+
+    // ---- conv1 + tanh + 2x2 max-pool for my two channels: one item = one pooling window -----------------------------
+    for (int it = t; it < 2 * 196; it += MN_T) {
+      const int c = it / 196, pos = it - c * 196, py = pos / 14, px = pos - py * 14;
+      float in[6][6];
+#pragma unroll
+      for (int dy = 0; dy < 6; ++dy)
+#pragma unroll
+        for (int dx = 0; dx < 6; ++dx) in[dy][dx] = s.x[(2 * py + dy) * 32 + 2 * px + dx];
+      float acc[4] = {s.b1[c], s.b1[c], s.b1[c], s.b1[c]};
+#pragma unroll
+      for (int ky = 0; ky < 5; ++ky)
+#pragma unroll
+        for (int kx = 0; kx < 5; ++kx) {
+          const float w = s.w1[c][ky * 5 + kx];
+          acc[0] = fmaf(w, in[ky][kx], acc[0]);
+          acc[1] = fmaf(w, in[ky][kx + 1], acc[1]);
+          acc[2] = fmaf(w, in[ky + 1][kx], acc[2]);
+          acc[3] = fmaf(w, in[ky + 1][kx + 1], acc[3]);
+        }
+      float best = -2.f;
+      int arg = 0;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const float v = tanhf(acc[k]);
+        s.a1[c][(2 * py + (k >> 1)) * 28 + 2 * px + (k & 1)] = v;
+        if (v > best) { best = v; arg = k; }      // first maximum in row-major order, like max_pool2d
+      }
+      s.i1[c][pos] = static_cast<unsigned char>(arg);
+#pragma unroll
+      for (int k = 0; k < MN_CL; ++k) peer[k]->p1[2 * r + c][pos] = best;   // all-gather through distributed shared memory
+    }
+    cluster.sync();   // [1] every CTA holds all 16 pooled maps
+
+    // ---- conv2 + tanh for my two output channels: thread = (co, output row, input channel) -------------------------
+    {
+      const int ci = t & 15, oy = (t >> 4) % 10, co = t / 160;
+      float acc[10];
+#pragma unroll
+      for (int ox = 0; ox < 10; ++ox) acc[ox] = 0.f;
+#pragma unroll
+      for (int ky = 0; ky < 5; ++ky) {
+        float row[14];
+#pragma unroll
+        for (int xx = 0; xx < 14; ++xx) row[xx] = s.p1[ci][(oy + ky) * 14 + xx];
+#pragma unroll
+        for (int kx = 0; kx < 5; ++kx) {
+          const float w = s.w2[co][ci][ky * 5 + kx];
+#pragma unroll
+          for (int ox = 0; ox < 10; ++ox) acc[ox] = fmaf(w, row[ox + kx], acc[ox]);
+        }
+      }
+#pragma unroll
+      for (int ox = 0; ox < 10; ++ox) {
+        const float v = warp_sum16(acc[ox]);      // over the 16 input channels, fixed butterfly order
+        if (ci == 0) s.a2[co][oy * 10 + ox] = tanhf(v + s.b2[co]);
+      }
+    }
+    __syncthreads();
+    if (t < 50) {  // 2x2 max-pool -> my 50 features
+      const int c = t / 25, pos = t - c * 25, py = pos / 5, px = pos - py * 5;
+      float best = -2.f;
+      int arg = 0;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const float v = s.a2[c][(2 * py + (k >> 1)) * 10 + 2 * px + (k & 1)];
+        if (v > best) { best = v; arg = k; }
+      }
+      s.p2[c][pos] = best;
+      s.i2[c][pos] = static_cast<unsigned char>(arg);
+    }
+    __syncthreads();
+    // ---- Linear: warp j forms my 50-feature part of logit j and hands it to every CTA ----------------------------
+    {
+      const int j = t >> 5, lane = t & 31;
+      const float* f = &s.p2[0][0];
+      float v = s.w3[j][lane] * f[lane] + (lane < 18 ? s.w3[j][32 + lane] * f[32 + lane] : 0.f);
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+      if (lane < MN_CL) peer[lane]->lpart[r][j] = v;
+    }
+    cluster.sync();   // [2] every CTA holds all partial logits
+
+    // ---- log-softmax, loss, dlogits: every CTA does the same sums in the same order -----------------------------
+    if (t == 0) {
+      float z[10], m = -INFINITY;
+#pragma unroll
+      for (int j = 0; j < 10; ++j) {
+        float v = s.b3[j];
+#pragma unroll
+        for (int k = 0; k < MN_CL; ++k) v += s.lpart[k][j];
+        z[j] = v;
+        m = fmaxf(m, v);
+      }
+      float sum = 0.f;
+#pragma unroll
+      for (int j = 0; j < 10; ++j) sum += expf(z[j] - m);
+      const float lse = m + logf(sum);
+      const long long yy = a.y[b];
+#pragma unroll
+      for (int j = 0; j < 10; ++j) {
+        const float lp = z[j] - lse;
+        s.dl[j] = (expf(lp) - (j == yy ? 1.f : 0.f)) * inv_b;       // d(mean NLL)/dlogit
+        if (r == 0 && a.logp != nullptr) a.logp[static_cast<long long>(b) * 10 + j] = lp;
+        if (j == yy) s.loss_acc -= lp;
+      }
+    }
+    __syncthreads();
+
+    // ---- Linear backward for my 50 features; un-pool and tanh' into conv2's pre-activation gradient ----------------
+    for (int i = t; i < 500; i += MN_T) {
+      const int j = i / 50, f = i - j * 50;
+      s.gw3[j][f] = fmaf(s.dl[j], (&s.p2[0][0])[f], s.gw3[j][f]);
+    }
+    if (t < 10) s.gb3[t] += s.dl[t];
+    if (t >= 32 && t < 82) {
+      const int f = t - 32;
+      float v = 0.f;
+#pragma unroll
+      for (int j = 0; j < 10; ++j) v = fmaf(s.dl[j], s.w3[j][f], v);
+      (&s.dfeat[0][0])[f] = v;
+    }
+    __syncthreads();
+    if (t < 200) {
+      const int c = t / 100, pos = t - c * 100, oy = pos / 10, ox = pos - oy * 10;
+      const int win = (oy >> 1) * 5 + (ox >> 1), k = ((oy & 1) << 1) | (ox & 1);
+      const float av = s.a2[c][pos];
+      const float up = s.i2[c][win] == k ? s.dfeat[c][win] : 0.f;
+      s.a2[c][pos] = up * (1.f - av * av);                            // now: gradient w.r.t. conv2's pre-activation
+    }
+    __syncthreads();
+
+    // ---- conv2 weight / bias gradients: thread = (co, ci, filter row), five taps each ---------------------------------
+    for (int it = t; it < 2 * 16 * 5; it += MN_T) {
+      const int co = it / 80, rem = it - co * 80, ci = rem / 5, ky = rem - ci * 5;
+      float acc[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
+      for (int oy = 0; oy < 10; ++oy) {
+        float row[14];
+#pragma unroll
+        for (int xx = 0; xx < 14; ++xx) row[xx] = s.p1[ci][(oy + ky) * 14 + xx];
+#pragma unroll
+        for (int ox = 0; ox < 10; ++ox) {
+          const float d = s.a2[co][oy * 10 + ox];
+#pragma unroll
+          for (int kx = 0; kx < 5; ++kx) acc[kx] = fmaf(d, row[ox + kx], acc[kx]);
+        }
+      }
+#pragma unroll
+      for (int kx = 0; kx < 5; ++kx) s.gw2[co][ci][ky * 5 + kx] += acc[kx];
+    }
+    if (t >= 160 && t < 162) {
+      const int co = t - 160;
+      float v = 0.f;
+      for (int i = 0; i < 100; ++i) v += s.a2[co][i];
+      s.gb2[co] += v;
+    }
+    // ---- conv2 input gradient: my two output channels' contribution to ALL 16 input channels, row by row ---------
+    for (int it = t; it < 16 * 14; it += MN_T) {
+      const int ci = it / 14, yy = it - ci * 14;
+      float acc[14];
+#pragma unroll
+      for (int xx = 0; xx < 14; ++xx) acc[xx] = 0.f;
+#pragma unroll
+      for (int co = 0; co < 2; ++co) {
+#pragma unroll
+        for (int ky = 0; ky < 5; ++ky) {
+          const int oy = yy - ky;
+          if (oy < 0 || oy > 9) continue;
+          float d[10];
+#pragma unroll
+          for (int ox = 0; ox < 10; ++ox) d[ox] = s.a2[co][oy * 10 + ox];
+#pragma unroll
+          for (int kx = 0; kx < 5; ++kx) {
+            const float w = s.w2[co][ci][ky * 5 + kx];
+#pragma unroll
+            for (int ox = 0; ox < 10; ++ox) acc[ox + kx] = fmaf(w, d[ox], acc[ox + kx]);
+          }
+        }
+      }
+      float* dst = &peer[ci >> 1]->dpart[r][ci & 1][yy * 14];         // reduce-scatter: slot r of the channel's owner
+#pragma unroll
+      for (int xx = 0; xx < 14; ++xx) dst[xx] = acc[xx];
+    }
+    cluster.sync();   // [3] my eight slots are filled
+
+    // ---- conv1 backward for my two channels: sum the slots, un-pool, tanh', then the filter gradients ----------------
+    for (int it = t; it < 2 * 196; it += MN_T) {
+      const int c = it / 196, pos = it - c * 196, py = pos / 14, px = pos - py * 14;
+      float dp = 0.f;
+#pragma unroll
+      for (int k = 0; k < MN_CL; ++k) dp += s.dpart[k][c][pos];        // rank order
+      const int arg = s.i1[c][pos];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        float* av = &s.a1[c][(2 * py + (k >> 1)) * 28 + 2 * px + (k & 1)];
+        *av = (k == arg) ? dp * (1.f - *av * *av) : 0.f;              // now: gradient w.r.t. conv1's pre-activation
+      }
+    }
+    __syncthreads();
+    // thread = (channel, filter tap, one of 4 row groups); the groups meet in fixed order through shared scratch (lpart
+    // and dfeat are free by now)
+    {
+      const int c = (t / 100) & 1, rem = t % 100, tap = rem >> 2, grp = rem & 3, ky = tap / 5, kx = tap - ky * 5;
+      float v = 0.f;
+      if (t < 200) {
+        for (int oy = grp * 7; oy < grp * 7 + 7; ++oy)
+          for (int ox = 0; ox < 28; ++ox) v = fmaf(s.a1[c][oy * 28 + ox], s.x[(oy + ky) * 32 + ox + kx], v);
+      }
+      v += __shfl_xor_sync(0xffffffffu, v, 1);     // whole warps take part (320 threads = 10 warps), idle lanes carry zeros
+      v += __shfl_xor_sync(0xffffffffu, v, 2);
+      if (t < 200 && grp == 0) s.gw1[c][tap] += v;
+      if (t >= 224 && t < 226) {
+        const int cb = t - 224;
+        float sum = 0.f;
+        for (int i = 0; i < 784; ++i) sum += s.a1[cb][i];
+        s.gb1[cb] += sum;
+      }
+    }
+    // No barrier here: the next sample's remote writes are ordered behind this sample's reads by the barriers themselves
+    // (p1 is last read before [3]; lpart right after [2]; dpart before a CTA reaches the next [1], and nobody writes
+    // dpart again before everybody has passed that [1] and the [2] after it).
+    __syncthreads();   // s.x and a1 are rewritten by the next sample
+  }
+
+  // ---- gradients out (or the update itself) ----------------------------------------------------------------------
+  __syncthreads();
+  const bool fused = a.apply_sgd != 0 && ncl == 1;
+  auto emit = [&](float* p, float* g, float grad) {
+    if (fused) {
+      *p = fmaf(-a.lr, grad, *p);        // same rounding as the flat-vector SGD kernels (csrc/fused_sgd.cu)
+    } else if (ncl == 1) {
+      *g += grad;                        // accumulate into .grad like autograd would
+    } else {
+      atomicAdd(g, grad);
+    }
+  };
+  for (int i = t; i < 50; i += MN_T) emit(a.p[0] + 2 * r * 25 + i, a.g[0] + 2 * r * 25 + i, (&s.gw1[0][0])[i]);
+  for (int i = t; i < 800; i += MN_T) emit(a.p[2] + 2 * r * 400 + i, a.g[2] + 2 * r * 400 + i, (&s.gw2[0][0][0])[i]);
+  for (int i = t; i < 500; i += MN_T) {
+    const int j = i / 50, f = i - j * 50, at = j * 400 + 2 * r * 25 + f;
+    emit(a.p[4] + at, a.g[4] + at, s.gw3[j][f]);
+  }
+  if (t < 2) {
+    emit(a.p[1] + 2 * r + t, a.g[1] + 2 * r + t, s.gb1[t]);
+    emit(a.p[3] + 2 * r + t, a.g[3] + 2 * r + t, s.gb2[t]);
+  }
+  if (r == 0 && t < 10) emit(a.p[5] + t, a.g[5] + t, s.gb3[t]);
+  if (r == 0 && t == 0) {
+    if (ncl == 1) *a.loss = s.loss_acc * inv_b;
+    else atomicAdd(a.loss, s.loss_acc * inv_b);
+  }
+  cluster.sync();   // no CTA may leave while a peer could still touch its shared memory
+}
+
+// x [B,1024] fp32, y [B] int64; params / grads: the six tensors of the model in module order.  apply_sgd != 0 (and a
+// batch small enough for one cluster, B <= DL_MNIST_FUSED_MAX_BATCH) fuses the update p -= lr * g into the launch and
+// leaves grads untouched; otherwise the gradient of the MEAN loss is ADDED into grads.  loss: 1 float (overwritten).
+extern "C" int dl_mnist_step(const float* x, const int64_t* y, float* const* params, float* const* grads, float* loss, float* logp,
+                             int B, float lr, int apply_sgd, void* stream) {
+  DL_REQUIRE(x && y && params && grads && loss && B > 0, "dl_mnist_step: bad arguments");
+  DL_REQUIRE(reinterpret_cast<uintptr_t>(x) % 16 == 0, "dl_mnist_step: x must be 16-byte aligned");
+  MnistArgs a;
+  a.x = x; a.y = reinterpret_cast<const long long*>(y); a.loss = loss; a.logp = logp; a.B = B; a.lr = lr;
+  for (int i = 0; i < 6; ++i) {
+    DL_REQUIRE(params[i] && grads[i], "dl_mnist_step: null parameter / gradient pointer");
+    a.p[i] = params[i];
+    a.g[i] = grads[i];
+  }
+  int ncl = B <= DL_MNIST_FUSED_MAX_BATCH ? 1 : (B + 3) / 4;       // a cluster walks ~4 samples when the batch is larger
+  const int cap = dl_sm_count() / MN_CL;
+  if (ncl > cap) ncl = cap;
+  a.apply_sgd = (apply_sgd && ncl == 1) ? 1 : 0;
+  DL_REQUIRE(!apply_sgd || ncl == 1, "dl_mnist_step: the fused update needs B <= %d (one cluster)", DL_MNIST_FUSED_MAX_BATCH);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  static bool configured = false;
+  if (!configured) {
+    DL_CUDA(cudaFuncSetAttribute(mnist_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(sizeof(MnistSmem))));
+    configured = true;
+  }
+  if (ncl > 1) DL_CUDA(cudaMemsetAsync(loss, 0, sizeof(float), st));
+  mnist_step_kernel<<<ncl * MN_CL, MN_T, sizeof(MnistSmem), st>>>(a);
+  dl_note_launch();
+  DL_CUDA(cudaGetLastError());
+  return DL_OK;
+}

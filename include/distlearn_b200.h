@@ -289,6 +289,16 @@ int dl_head_fwd(const float* feat, const float* w, const float* bias, const int6
 int dl_head_bwd(const float* feat, const float* w, const float* logp, const int64_t* target, const float* gloss, float* dfeat,
                 float* dw, float* db, int B, int HW, int C, int J, int accumulate, void* stream);
 
+/* One training step of the reference's MNIST network (examples/mnist.lua:53-81: conv 1->16 5x5, tanh, maxpool, conv 16->16
+ * 5x5, tanh, maxpool, Linear 400->10, logSoftMax + NLL) as ONE launch of an 8-CTA thread-block cluster (csrc/mnist_step.cu):
+ * forward, backward and - with apply_sgd != 0 and B <= DL_MNIST_FUSED_MAX_BATCH - the update p -= lr * g of
+ * examples/mnist.lua:112-116.  x [B,1024] fp32, y [B] int64; params / grads: the six tensors in module order (conv1.weight,
+ * conv1.bias, conv2.weight, conv2.bias, linear.weight, linear.bias).  Without the fused update the gradient of the mean
+ * loss is ADDED into grads.  loss: 1 float; logp: [B,10] log-probabilities or NULL. */
+#define DL_MNIST_FUSED_MAX_BATCH 8
+int dl_mnist_step(const float* x, const int64_t* y, float* const* params, float* const* grads, float* loss, float* logp, int B,
+                  float lr, int apply_sgd, void* stream);
+
 /* ---- local flat-vector ops (single GPU, no communication) ---- */
 /* p -= lr * (g*scale [+ wd*p] [momentum]); optionally zero g. world==1 fast path. */
 int dl_local_sgd(float* p, float* g, float* m, uint64_t n, float lr, float momentum,

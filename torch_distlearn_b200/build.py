@@ -36,6 +36,7 @@ CUDA_SOURCES = [
     "ll_ops.cu",
     "litmus.cu",
     "peak.cu",
+    "mnist_step.cu",
     "tc_gemm.cu",
     "conv_ops.cu",
     "bn_ops.cu",
