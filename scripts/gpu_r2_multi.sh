@@ -30,4 +30,8 @@ echo "benches done ($(( $(date +%s) - t0 ))s)"
 for impl in ours ours_eager hostloop; do
 timeout 150 $TR --master-port 29547 bench/bench_async.py --impl $impl --steps 100 > gpurun_out/r2_async${N}_$impl.log 2>&1; echo "async $impl rc=$? $(tail -n 1 gpurun_out/r2_async${N}_$impl.log | cut -c1-300)"
 done
+for impl in ours nccl; do
+timeout 120 $TR --master-port 29546 bench/bench_ea.py --impl $impl --batch 1 --steps 2000 > gpurun_out/r2_mnist_ea${N}_$impl.log 2>&1; echo "mnist ea $impl rc=$? $(tail -n 1 gpurun_out/r2_mnist_ea${N}_$impl.log | cut -c1-300)"
+done
+timeout 120 $TR --master-port 29546 bench/bench_ea.py --impl ours --fused 0 --batch 1 --steps 2000 > gpurun_out/r2_mnist_ea${N}_ours_unfused.log 2>&1; echo "mnist ea ours unfused rc=$? $(tail -n 1 gpurun_out/r2_mnist_ea${N}_ours_unfused.log | cut -c1-300)"
 echo "total $(( $(date +%s) - t0 ))s"
