@@ -67,7 +67,8 @@ def parse():
     p.add_argument("--bucket-mb", type=float, default=None,
                    help="ours: launch the fused kernel per gradient bucket of this size, overlapped with backward "
                         "(0 = one launch after backward; default: 0.5 for N > 1 = one bucket per layer of this model)")
-    p.add_argument("--bucket-blocks", type=int, default=32, help="CTAs per bucket launch (leaves the other SMs to the convolutions)")
+    p.add_argument("--bucket-blocks", type=int, default=0,
+                   help="CTAs per bucket launch (0 = one light CTA per SM, beside the convolution's CTA)")
     a = p.parse_args()
     if a.graph is None:
         a.graph = 1 if a.impl == "ours" else 0

@@ -188,3 +188,76 @@ __device__ __forceinline__ void dl_pipe_foreach_released(unsigned long long n4, 
     for (unsigned long long k = b4 + threadIdx.x; k < e4; k += DL_PIPE_THREADS) fn(k);
   }
 }
+
+// ---- the LIGHT slice pass: made to run UNDER the convolutions -------------------------------------------------------
+// A gradient bucket that is reduced while backward is still running shares the SMs with the tensor-core GEMM, whose
+// persistent CTA (576 threads x 96 registers, ~200 KB of shared memory) leaves 10,240 registers and ~25 KB of shared
+// memory per SM.  The kernels above (256 threads x 192 registers) cannot move in beside it: they wait for whole SMs to
+// drain, and then keep the next GEMM's CTAs out in turn — which is why per-bucket launches gained 1 % in round 1.
+// The light pass is sized to fit the gap instead: DL_LIGHT_THREADS threads of at most 80 registers, one 16-byte vector
+// per source in flight per thread and no double buffering — the bytes in flight come from running on ALL SMs at once
+// (148 x 128 threads x 8 sources x 16 B = 2.4 MB, the bandwidth-delay product of the links).
+#define DL_LIGHT_THREADS 128
+#define DL_LIGHT_MC_U 4
+
+template <int W, typename Epi>
+__device__ __forceinline__ void dl_light_p2p(const dl_comm_t& c, int world, uint32_t lmask, uint64_t src_off, uint64_t dst_off,
+                                             unsigned long long begin4, unsigned long long end4, Epi& epi) {
+  const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+  for (unsigned long long i = begin4 + threadIdx.x; i < end4; i += DL_LIGHT_THREADS) {
+    float4 v[W];
+#pragma unroll
+    for (int j = 0; j < W; ++j) v[j] = (j < world && ((lmask >> j) & 1u)) ? dl_ld_f4(dl_at<float4>(c, j, src_off) + i) : z;
+    const float4 out = epi.p2p(v, i);
+#pragma unroll
+    for (int j = 0; j < W; ++j)
+      if (j < world) dl_st_f4(dl_at<float4>(c, j, dst_off) + i, out);
+  }
+}
+
+template <typename Epi>
+__device__ __forceinline__ void dl_light_mc(const dl_comm_t& c, uint64_t src_off, uint64_t dst_off, unsigned long long begin4,
+                                            unsigned long long end4, Epi& epi) {
+  constexpr int U = DL_LIGHT_MC_U;
+  const float4* msrc = dl_mc_at<float4>(c, src_off);
+  float4* mdst = dl_mc_at<float4>(c, dst_off);
+  for (unsigned long long i0 = begin4 + threadIdx.x; i0 < end4; i0 += static_cast<unsigned long long>(U) * DL_LIGHT_THREADS) {
+    float4 v[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const unsigned long long idx = i0 + static_cast<unsigned long long>(u) * DL_LIGHT_THREADS;
+      if (idx < end4) v[u] = dl_mc_ld_reduce_f4(msrc + idx);
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const unsigned long long idx = i0 + static_cast<unsigned long long>(u) * DL_LIGHT_THREADS;
+      if (idx < end4) dl_mc_st_f4(mdst + idx, epi.mc(v[u], idx));
+    }
+  }
+}
+
+template <int W, typename Epi>
+__device__ __forceinline__ void dl_light_pass(const dl_comm_t& c, int world, uint32_t lmask, bool full, int permille, uint64_t src_off,
+                                              uint64_t dst_off, const DlSlice& s, Epi& epi) {
+  const DlPipeRange g = dl_pipe_range(s.slice4, static_cast<int>(gridDim.x), static_cast<int>(blockIdx.x),
+                                      (full && c.mc != nullptr) ? permille : 0);
+  unsigned long long b4 = s.begin + g.r0, e4 = s.begin + g.r1;
+  if (b4 > s.end) b4 = s.end;
+  if (e4 > s.end) e4 = s.end;
+  if (g.nvls) dl_light_mc(c, src_off, dst_off, b4, e4, epi);
+  else dl_light_p2p<W>(c, world, lmask, src_off, dst_off, b4, e4, epi);
+}
+
+template <typename Fn>
+__device__ __forceinline__ void dl_light_foreach_released(unsigned long long n4, int world, bool full, bool has_mc, int permille,
+                                                          const DlSlice& s, Fn fn) {
+  const DlPipeRange g = dl_pipe_range(s.slice4, static_cast<int>(gridDim.x), static_cast<int>(blockIdx.x),
+                                      (full && has_mc) ? permille : 0);
+  for (int j = 0; j < world; ++j) {
+    const unsigned long long base = s.slice4 * static_cast<unsigned long long>(j);
+    unsigned long long b4 = base + g.r0, e4 = base + g.r1;
+    if (b4 > n4) b4 = n4;
+    if (e4 > n4) e4 = n4;
+    for (unsigned long long k = b4 + threadIdx.x; k < e4; k += DL_LIGHT_THREADS) fn(k);
+  }
+}

@@ -208,6 +208,35 @@ __global__ void __launch_bounds__(DL_PIPE_THREADS, 1) sgd_pipe_kernel(dl_comm_t 
   }
 }
 
+// ---- DL_VARIANT_LIGHT: the per-bucket kernel that runs beside the convolutions (dl_pipe.cuh, "light slice pass") ----
+template <int kWorld, bool kEmu>
+__global__ void __launch_bounds__(DL_LIGHT_THREADS, 6) sgd_light_kernel(dl_comm_t c, SgdArgs a) {
+  __shared__ uint32_t pay[DL_MAX_RANKS];
+  __shared__ uint32_t auxs[DL_MAX_RANKS];
+  constexpr int W = kWorld ? kWorld : DL_MAX_RANKS;
+  const int rank = kEmu ? static_cast<int>(blockIdx.y) : c.rank;
+  const int world = kWorld ? kWorld : c.world;
+  const int act = kEmu ? ((a.active >> rank) & 1u) : (a.active & 3u);
+  const uint32_t user = kEmu ? a.payload + rank : a.payload;
+  const bool ok = dl_block_barrier<false>(c, rank, world, a.channel, dl_pack_payload(act, user), pay, __float_as_uint(a.lr), auxs);
+  int n_act;
+  const uint32_t mask = dl_active_mask(c, rank, world, a.channel, pay, &n_act);
+  a.lr = __uint_as_float(dl_aux_of_first_active(mask, auxs, rank));
+  const DlSlice s = dl_slice_even(a.n4, rank, world);
+  const bool full = n_act == world;
+  if (ok && n_act > 0) {
+    SgdEpi<W> epi{a, dl_at<float4>(c, rank, a.p_off), a.m_off ? dl_at<float4>(c, rank, a.m_off) : nullptr,
+                  n_act > 1 ? 1.f / static_cast<float>(n_act) : 1.f};
+    dl_light_pass<W>(c, world, mask, full, c.nvls_permille, a.g_off, a.p_off, s, epi);
+  }
+  const bool ok2 = dl_block_barrier(c, rank, world, a.channel, 0u, pay);
+  if (ok && ok2 && a.zero_grads) {
+    float4* g_loc = dl_at<float4>(c, rank, a.g_off);
+    const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+    dl_light_foreach_released(a.n4, world, full, c.mc != nullptr, c.nvls_permille, s, [&](unsigned long long k) { g_loc[k] = z; });
+  }
+}
+
 template <int kWorld, bool kEmu>
 __global__ void __launch_bounds__(DL_THREADS, 1) sgd_oneshot_kernel(dl_comm_t c, SgdArgs a) {
   __shared__ uint32_t pay[DL_MAX_RANKS];
@@ -324,6 +353,26 @@ extern "C" int dl_fused_sgd(const dl_comm_t* c, uint64_t g_off, uint64_t p_off, 
   if (nb < 0) return nb;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   int rc = DL_OK;
+  if (variant == DL_VARIANT_LIGHT) {
+    DL_REQUIRE(n % 8 == 0, "dl_fused_sgd: the light variant needs n %% 8 == 0 (even slices)");
+    DL_REQUIRE(c->nvls_permille >= 0 && c->nvls_permille <= 1000, "dl_fused_sgd: nvls_permille out of range");
+    DL_REQUIRE(c->nvls_permille == 0 || (c->mc && !c->emulate), "dl_fused_sgd: nvls_permille > 0 needs a multicast mapping");
+    // one small CTA per SM at most: they move in beside the convolution's CTAs; ~4 vectors per thread at least
+    nb = dl_check_comm(c, channel, dl_pick_blocks(work / 4 + 1, 1, nblocks));
+    if (nb < 0) return nb;
+#define DL_SGD_LIGHT(WORLD)                                                                                     \
+    rc = c->emulate ? dl_launch(sgd_light_kernel<WORLD, true>, c, nb, DL_LIGHT_THREADS, st, *c, a)                \
+                    : dl_launch(sgd_light_kernel<WORLD, false>, c, nb, DL_LIGHT_THREADS, st, *c, a)
+    switch (c->world) {
+      case 1: DL_SGD_LIGHT(1); break;
+      case 2: DL_SGD_LIGHT(2); break;
+      case 4: DL_SGD_LIGHT(4); break;
+      case 8: DL_SGD_LIGHT(8); break;
+      default: DL_SGD_LIGHT(0); break;
+    }
+#undef DL_SGD_LIGHT
+    return rc;
+  }
   if (variant == DL_VARIANT_HYBRID) {
     DL_REQUIRE(n % 8 == 0 && g_off % 32 == 0 && p_off % 32 == 0 && m_off % 32 == 0,
                "dl_fused_sgd: the hybrid variant moves 32 bytes at a time: n %% 8 == 0 and 32-byte aligned offsets");

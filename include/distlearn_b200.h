@@ -41,6 +41,9 @@ extern "C" {
                                 switch (multimem) and the rest over P2P loads in the same launch; nvls_permille
                                 in dl_comm_t sets the split (0 = all P2P, 1000 = all NVLS) */
 
+#define DL_VARIANT_LIGHT 5   /* fused_sgd only: the hybrid pass in small CTAs (128 threads, <= 80 registers) that fit on an SM
+                                beside the tensor-core GEMM's CTA - the variant gradient buckets use under backward */
+
 /* dl_comm_t.flags */
 #define DL_FLAG_DEBUG 1u     /* barriers check epoch monotonicity / slot contents and report DL_EPROTO */
 

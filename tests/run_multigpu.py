@@ -37,9 +37,10 @@ def rand(n, seed):
 
 def kernel_checks(comm, rank, world, dev, quick):
     # (variant, share of every slice that goes through the switch): the hybrid kernel is checked all-P2P, mixed and all-switch
-    variants = [("ll", 0), ("oneshot", 0), ("twoshot", 0), ("hybrid", 0)]
+    # ("light" is a fused_sgd variant — the per-bucket kernel — the other operations run their two-shot form under that name)
+    variants = [("ll", 0), ("oneshot", 0), ("twoshot", 0), ("hybrid", 0), ("light", 0)]
     if comm.has_multicast:
-        variants += [("nvls", 0), ("hybrid", 600), ("hybrid", 1000)]
+        variants += [("nvls", 0), ("hybrid", 600), ("hybrid", 1000), ("light", 600)]
     sizes = [256, 40000, 1 << 20] if quick else [64, 4128, 40000, 1 << 20, (1 << 24) + 64]
     nmax = max(sizes)
     buf = comm.alloc(nmax, torch.float32, "chk.a")

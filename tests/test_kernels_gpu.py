@@ -93,7 +93,7 @@ def test_allreduce_inactive_and_normalise(variant):
 
 
 @pytest.mark.parametrize("world", [1, 2, 4, 8, 5])
-@pytest.mark.parametrize("variant", ["oneshot", "twoshot", "hybrid", "ll"])
+@pytest.mark.parametrize("variant", ["oneshot", "twoshot", "hybrid", "light", "ll"])
 @pytest.mark.parametrize("momentum,wd,nesterov", [(0.0, 0.0, False), (0.9, 1e-3, False), (0.9, 0.0, True)])
 def test_fused_sgd(world, variant, momentum, wd, nesterov):
     n, lr = 50016, 0.05

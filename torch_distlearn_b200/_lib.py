@@ -21,9 +21,9 @@ DL_EPROTO = -6
 DL_FLAG_DEBUG = 1
 DL_HOST_RING = 64
 
-VARIANT_ONESHOT, VARIANT_TWOSHOT, VARIANT_NVLS, VARIANT_LL, VARIANT_HYBRID = 0, 1, 2, 3, 4
+VARIANT_ONESHOT, VARIANT_TWOSHOT, VARIANT_NVLS, VARIANT_LL, VARIANT_HYBRID, VARIANT_LIGHT = 0, 1, 2, 3, 4, 5
 VARIANT_NAMES = {"oneshot": VARIANT_ONESHOT, "twoshot": VARIANT_TWOSHOT, "nvls": VARIANT_NVLS, "ll": VARIANT_LL,
-                 "hybrid": VARIANT_HYBRID}
+                 "hybrid": VARIANT_HYBRID, "light": VARIANT_LIGHT}
 DT_F32, DT_I32, DT_I64, DT_F64 = 0, 1, 2, 3
 
 

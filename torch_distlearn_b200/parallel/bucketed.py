@@ -5,8 +5,11 @@ another (examples/cifar10.lua:181-191).  Here the flat gradient vector is cut in
 buckets in *backward order* (last layer first).  As soon as autograd has accumulated the last
 gradient of a bucket, a post-accumulate hook records an event on the compute stream and launches
 ``fused_allreduce_normalize_sgd`` for that slice of the flat vector on a side stream, with a capped
-number of CTAs so cuDNN keeps most SMs: communication and the parameter update of layer L run under
-the backward kernels of layers < L.  Buckets are always launched in the same fixed order on every
+number of CTAs: communication and the parameter update of layer L run under the backward kernels of layers < L.
+On the CUDA backends the launches use the LIGHT variant of the kernel (128 threads, <= 80 registers per CTA): small
+enough to sit on an SM next to the tensor-core GEMM's persistent CTA, so that the bucket really runs beside the
+convolutions instead of queueing for whole SMs (csrc/dl_pipe.cuh); buckets below the small-message limit take the
+push path (one NVLink crossing, no barrier).  Buckets are always launched in the same fixed order on every
 rank (a bucket that becomes ready early waits for its predecessors), because every rank must issue
 the same sequence of collective kernels.  The whole fork/join pattern is capturable in a CUDA graph.
 """
@@ -25,7 +28,7 @@ class _Bucket:
 
 
 class GradBuckets:
-    def __init__(self, flat: FlatParams, sgd: AllReduceSGD, bucket_mb: float = 8.0, nblocks: int = 32, channel: int = 2,
+    def __init__(self, flat: FlatParams, sgd: AllReduceSGD, bucket_mb: float = 8.0, nblocks: int = 0, channel: int = 2,
                  variant: str = "auto"):
         if flat.grads is None:
             raise ValueError("GradBuckets needs FlatParams with gradients")
@@ -95,8 +98,11 @@ class GradBuckets:
     def _launch(self, b: _Bucket, active: int) -> None:
         h = self._hyper
         payload = min(self.sgd.steps + (1 if active else 0), 2**30 - 1)
+        variant = self.variant
+        if variant == "auto" and self.stream is not None and b.numel * 4 > getattr(self.comm, "ll_max_bytes", 0):
+            variant = "light"            # shares the SMs with the backward kernels it overlaps
         kw = dict(momentum=h["momentum"], weight_decay=h["weight_decay"], nesterov=h["nesterov"], active=active,
-                  payload=payload, zero_grads=True, variant=self.variant, channel=self.channel, read=False)
+                  payload=payload, zero_grads=True, variant=variant, channel=self.channel, read=False)
         mom = b.momentum if h["momentum"] != 0.0 else None
         if self.stream is None:
             self.comm.fused_sgd(b.grads, b.params, mom, b.numel, h["lr"], **kw)

@@ -28,11 +28,11 @@ from typing import List, Optional
 import torch
 
 from .. import _lib
-from .._lib import (DL_PAD_BYTES, DlComm, DlHostWords, DlResult, VARIANT_HYBRID, VARIANT_LL, VARIANT_NAMES, VARIANT_NVLS,
-                    VARIANT_ONESHOT, VARIANT_TWOSHOT)
+from .._lib import (DL_PAD_BYTES, DlComm, DlHostWords, DlResult, VARIANT_HYBRID, VARIANT_LIGHT, VARIANT_LL, VARIANT_NAMES,
+                    VARIANT_NVLS, VARIANT_ONESHOT, VARIANT_TWOSHOT)
 
 VARIANT_TEXT = {VARIANT_ONESHOT: "oneshot", VARIANT_TWOSHOT: "twoshot", VARIANT_NVLS: "nvls", VARIANT_LL: "ll",
-                VARIANT_HYBRID: "hybrid"}
+                VARIANT_HYBRID: "hybrid", VARIANT_LIGHT: "light"}
 _ALIGN = 512  # byte alignment of every symmetric allocation (>= 16 for 128-bit access)
 
 _DTYPE_CODES = {torch.float32: _lib.DT_F32, torch.int32: _lib.DT_I32, torch.int64: _lib.DT_I64,
@@ -170,6 +170,8 @@ class _VariantTable:
                 v = VARIANT_TWOSHOT
             if v == VARIANT_HYBRID and (not aligned32 or op == "broadcast"):
                 v = VARIANT_NVLS if (has_mc and world > 2) else VARIANT_TWOSHOT
+            if v == VARIANT_LIGHT and (not aligned32 or op != "fused_sgd"):
+                v = VARIANT_TWOSHOT
             return v
         if world > 1 and nbytes <= min(self.ll_max.get(op, 0), ll_cap):
             return VARIANT_LL

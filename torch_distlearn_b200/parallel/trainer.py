@@ -27,7 +27,7 @@ class TrainStep:
                  lr: float, momentum: float = 0.0, weight_decay: float = 0.0, nesterov: bool = False,
                  loss_fn: Optional[Callable] = None, use_graph: bool = True, variant: str = "auto",
                  target_dtype: torch.dtype = torch.int64, warmup: int = 3, nblocks: int = 0, bucket_mb: float = 0.0,
-                 bucket_blocks: int = 32, restore_warmup: bool = True):
+                 bucket_blocks: int = 0, restore_warmup: bool = True):
         self.model, self.flat, self.sgd = model, flat, sgd
         self.lr, self.momentum, self.weight_decay, self.nesterov = lr, momentum, weight_decay, nesterov
         self._fused_loss = loss_fn is None and hasattr(model, "forward_with_loss")
