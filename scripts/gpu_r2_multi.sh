@@ -15,7 +15,7 @@ grep "variant table" gpurun_out/r2_sweep_$N.log | cut -c1-400
 timeout 300 $TR --master-port 29542 bench/sweep.py --max-mb 64 --permille 0,750,1000 --graph --write-table --out gpurun_out/r2_sweep_${N}_graph.json > gpurun_out/r2_sweep_${N}_graph.log 2>&1; echo "sweep graph rc=$? ($(( $(date +%s) - t0 ))s)"
 grep "variant table" gpurun_out/r2_sweep_${N}_graph.log | cut -c1-400
 # install the freshly measured table for the benches below (world N entry)
-python scripts/merge_variant_table.py gpurun_out/variant_table_$N.json $N; echo "table merge rc=$?"
+python scripts/merge_variant_table.py gpurun_out/variant_table_${N}_graph.json $N; echo "table merge rc=$?"
 b() { name=$1; shift; timeout 200 $TR --master-port 29551 bench.py --gpus $N --steps 100 --warmup 10 "$@" > gpurun_out/r2_bench${N}_$name.log 2>&1; echo "bench $name rc=$? $(tail -n 1 gpurun_out/r2_bench${N}_$name.log | cut -c1-160)"; }
 b b0 --baselines 0 --bucket-mb 0
 b mod05 --baselines 0 --bucket-mb 0.5 --flat-order module
