@@ -25,7 +25,9 @@ def main(paths):
         print(f"## {path.split('/')[-1]} — {world} x B200, transport {d['transport']['mode']}, "
               f"multicast={d['transport']['multicast']}, timing={'CUDA-graph replay' if graph else 'eager launches'}\n")
         print(f"Per cell: time per call in us (max over ranks) / bus bandwidth GB/s / fraction of that variant's own "
-              f"NVLink roofline at {d['link_gbs']:.0f} GB/s per direction.  `nccl` = torch.distributed NCCL doing the same "
+              f"NVLink roofline at {d['link_gbs']:.0f} GB/s per direction ({d.get('link_gbs_source', 'recipe constant')}).  "
+              f"`ll` = push path (no barrier), `hybridP` = pipelined slice pass with P/1000 of every slice reduced in the "
+              f"switch and the rest over 256-bit P2P loads.  `nccl` = torch.distributed NCCL doing the same "
               f"work (all_reduce AVG + p.add_ for fused_sgd; 3 elementwise ops + all_reduce + add for fused_ea).\n")
         t = collections.defaultdict(dict)
         for r in rows:
@@ -34,7 +36,9 @@ def main(paths):
             sizes = sorted(b for (o, b) in t if o == op)
             if not sizes:
                 continue
-            impls = [i for i in ("oneshot", "twoshot", "nvls", "nccl") if any(i in t[(op, b)] for b in sizes)]
+            seen = {i for b in sizes for i in t[(op, b)]}
+            hybrids = sorted((i for i in seen if i.startswith("hybrid")), key=lambda i: int(i[6:]))
+            impls = [i for i in ["ll", "oneshot", "twoshot", "nvls"] + hybrids + ["nccl"] if i in seen]
             print(f"### {op}\n")
             print("| bytes | " + " | ".join(impls) + " | best ours / nccl |")
             print("|---|" + "---|" * (len(impls) + 1))
