@@ -52,6 +52,32 @@ def forward_backward(model, batch):
     return out.detach(), loss.detach()
 
 
+class MnistKernelStep:
+    """forward + backward of the MNIST network as ONE kernel (csrc/mnist_step.cu, an 8-CTA cluster) instead of ~25 small
+    library kernels; with ``lr`` given (and a batch of at most 8) the plain SGD update is fused in as well.  Returns
+    what ``forward_backward`` returns: (log-probabilities, loss), both on the device."""
+
+    def __init__(self, model, batch_size: int):
+        from torch_distlearn_b200.ops.mnist import model_tensors
+        self.params, self.grads = model_tensors(model)
+        dev = self.params[0].device
+        self.loss = torch.zeros(1, device=dev)
+        self.logp = torch.zeros(batch_size, 10, device=dev)
+
+    @staticmethod
+    def usable(model, device, batch_size: int) -> bool:
+        return device.type == "cuda" and type(model).__name__ == "MnistConvNet" and batch_size <= 4096
+
+    def __call__(self, batch, lr=None):
+        from torch_distlearn_b200.ops.mnist import FUSED_MAX_BATCH, mnist_step
+        B = batch.input.shape[0]
+        fuse = lr is not None and B <= FUSED_MAX_BATCH
+        x = batch.input.reshape(B, 1024).contiguous()
+        mnist_step(x, batch.target.to(torch.int64).contiguous(), self.params, self.grads, self.loss, self.logp[:B],
+                   lr=lr or 0.0, apply_sgd=fuse)
+        return self.logp[:B], self.loss[0], fuse
+
+
 @torch.no_grad()
 def evaluate(model, get_batch, n_batches: int, confusion, batch_stats: bool = False) -> float:
     """Mean loss over ``n_batches``.  ``batch_stats`` keeps BatchNorm on batch statistics: a model that

@@ -5,7 +5,7 @@ Every node runs plain local SGD; every ``tau`` steps ``averageParameters`` pulls
 shared center and the center towards the nodes (tau=10, alpha=0.2 as shipped, examples/mnist-ea.lua:18).
 Here that call is one fused kernel (csrc/fused_ea.cu).  Epoch end: ``synchronizeCenter`` (:121).
 """
-from common import batches_this_epoch, forward_backward, setup, Throughput
+from common import batches_this_epoch, forward_backward, setup, Throughput, MnistKernelStep
 
 import torch_distlearn_b200 as dl
 from torch_distlearn_b200.launch import shutdown
@@ -20,6 +20,7 @@ def main(argv=None):
     p = base_parser("MNIST AllReduceEA (examples/mnist-ea.lua)", batch_size=1, learning_rate=0.01)
     p.add_argument("--tau", "--communicationTime", dest="tau", type=int, default=10)
     p.add_argument("--alpha", type=float, default=0.2)
+    p.add_argument("--eager", action="store_true", help="stock torch kernels for forward/backward instead of the one-launch step")
     opt = p.parse_args(argv)
     comm, log = setup(opt)
     dev = comm.device
@@ -37,13 +38,23 @@ def main(argv=None):
     cm = ConfusionMatrix(MNIST_CLASSES, comm=comm)
     n_batches = batches_this_epoch(num_batches(), opt)
     use_kernel = dev.type == "cuda"
+    kstep = None
+    if MnistKernelStep.usable(model, dev, opt.batchSize) and not opt.eager:
+        kstep = MnistKernelStep(model, opt.batchSize)              # the whole local step in one launch (csrc/mnist_step.cu)
     for epoch in range(1, opt.numEpochs + 1):
         cm.zero()
         thr, loss_sum = Throughput(), 0.0
         for _ in range(n_batches):
             batch = get_batch()
-            out, loss = forward_backward(model, batch)
-            if use_kernel:                                         # local SGD (examples/mnist-ea.lua:103-107)
+            done = False
+            if kstep is not None and batch.input.shape[0] == opt.batchSize:
+                plain = opt.momentum == 0 and opt.weightDecay == 0
+                out, loss, done = kstep(batch, lr=opt.learningRate if plain else None)
+            else:
+                out, loss = forward_backward(model, batch)
+            if done:                                               # gradient and update happened in the same kernel
+                pass
+            elif use_kernel:                                       # local SGD (examples/mnist-ea.lua:103-107)
                 local_sgd(flat.params.tensor, flat.grads.tensor, flat.momentum.tensor if flat.momentum else None,
                           lr=opt.learningRate, momentum=opt.momentum, weight_decay=opt.weightDecay, zero_grads=True)
             else:
