@@ -114,4 +114,4 @@ def test_streamk_whole_model_step(streamk):
     # because the split-K partial tiles meet in red.add order)
     torch.testing.assert_close(outs[1][2], outs[0][2], rtol=1e-4, atol=1e-5)
     torch.testing.assert_close(outs[1][0], outs[0][0], rtol=1e-2, atol=5e-4)
-    torch.testing.assert_close(torch.tensor(outs[1][1]), torch.tensor(outs[0][1]), rtol=1e-4, atol=1e-4)
+    torch.testing.assert_close(torch.tensor(outs[1][1]), torch.tensor(outs[0][1]), rtol=1e-3, atol=1e-3)

@@ -225,8 +225,12 @@ def test_ea_trainstep_matches_the_written_out_loop(use_graph):
         step.step(x, y)
     torch.cuda.synchronize()
     assert ea.step == len(batches) and step.sgd.steps == len(batches)
-    torch.testing.assert_close(flat.params.tensor, p_ref, rtol=1e-5, atol=1e-5)
-    torch.testing.assert_close(ea.center, c_ref, rtol=1e-5, atol=1e-5)
+    # Two separate runs of the tensor-core model: the split-K / stream-K partial tiles of the weight-gradient GEMMs meet
+    # in red.add order, which differs from run to run, and seven steps at lr 0.01 on random labels amplify that seed
+    # (measured on a B200: 1.6e-4 between the two eager runs, < 1e-5 when both happen to add in the same order).  A wrong
+    # elastic move or a misplaced SGD step is off by 1e-2 and more.
+    torch.testing.assert_close(flat.params.tensor, p_ref, rtol=1e-3, atol=5e-4)
+    torch.testing.assert_close(ea.center, c_ref, rtol=1e-3, atol=5e-4)
     assert step.loss_value() == step.loss_value()
 
 
@@ -268,8 +272,9 @@ def test_async_trainstep_matches_the_reference_order(use_graph):
         step.step(x, y)
     torch.cuda.synchronize()
     assert comm.sync_count(0) == len(batches) // tau
-    torch.testing.assert_close(flat.params.tensor, p_ref, rtol=1e-5, atol=1e-5)
-    torch.testing.assert_close(server._center.tensor[:flat.numel], c_ref[:flat.numel], rtol=1e-5, atol=1e-5)
+    # (same run-to-run freedom of the weight-gradient GEMMs as in the EA test above)
+    torch.testing.assert_close(flat.params.tensor, p_ref, rtol=1e-3, atol=5e-4)
+    torch.testing.assert_close(server._center.tensor[:flat.numel], c_ref[:flat.numel], rtol=1e-3, atol=5e-4)
 
 
 def test_set_lr_takes_effect_on_the_graph_path():
