@@ -55,9 +55,22 @@ __global__ void __launch_bounds__(BN_THREADS) bn_stats_kernel(const float4* __re
 // thread per channel walking all ~300 partial rows alone took 20-40 us per call; this takes a few.
 #define FIN_X 32
 #define FIN_Y 16
+// reductions use two blocks per SM at most: each block leaves one partial row, summed by a finalize kernel
+#define BN_MAX_REDUCE_BLOCKS 296
+// All of a thread's partial rows are loaded before the first add: the loads are independent, so the kernel costs ONE
+// memory round trip instead of nblocks / FIN_Y dependent ones (ncu: 17 us for a 128-channel finalize, nearly all of it
+// waiting on 19 loads in a row; profiles/ncu_kernels_r2.md).  Same summation order as before.
+#define FIN_MAX_ROWS ((BN_MAX_REDUCE_BLOCKS + FIN_Y - 1) / FIN_Y)
 __device__ __forceinline__ double fin_sum(const float* partial, int nblocks, long long row_stride, int c, double (*sh)[FIN_X]) {
+  float v[FIN_MAX_ROWS];
+#pragma unroll
+  for (int k = 0; k < FIN_MAX_ROWS; ++k) {
+    const int b = threadIdx.y + k * FIN_Y;
+    v[k] = b < nblocks ? __ldcg(partial + static_cast<long long>(b) * row_stride + c) : 0.f;
+  }
   double a = 0.0;
-  for (int b = threadIdx.y; b < nblocks; b += FIN_Y) a += static_cast<double>(partial[static_cast<long long>(b) * row_stride + c]);
+#pragma unroll
+  for (int k = 0; k < FIN_MAX_ROWS; ++k) a += static_cast<double>(v[k]);
   sh[threadIdx.y][threadIdx.x] = a;
   __syncthreads();
   double t = 0.0;
@@ -276,8 +289,7 @@ static int bn_grid(long long items, int per_block) {
   return nb < 1 ? 1 : static_cast<int>(nb);
 }
 
-// reductions use one block per SM pair at most: each block leaves one partial row, summed by a finalize kernel
-#define BN_MAX_REDUCE_BLOCKS 296
+// (BN_MAX_REDUCE_BLOCKS is defined next to the finalize kernels above)
 static int bn_reduce_grid(long long rows, int rows_per_pass) {
   long long nb = (rows + static_cast<long long>(rows_per_pass) * 8 - 1) / (static_cast<long long>(rows_per_pass) * 8);
   if (nb > BN_MAX_REDUCE_BLOCKS) nb = BN_MAX_REDUCE_BLOCKS;

@@ -97,6 +97,24 @@ def main():
 
         add(f"{tag} conv forward+backward", timed_graph(conv_fwd_bwd, args.reps))
 
+        if li > 0:      # the three implicit GEMMs one by one, fp32-accurate (3xTF32) and plain TF32
+            TAPS = 25
+            yo = torch.empty(M, cout, device=dev)
+            dxo = torch.empty(B, H, H, cin, device=dev)
+            dwo = torch.zeros(cout, TAPS * cin, device=dev)
+            dyc = dy.contiguous()
+            flop = 2.0 * M * cout * TAPS * cin
+            for terms in (3, 1):
+                sp_f = convops._splits((M + 127) // 128, (cout + 127) // 128, TAPS * cin)
+                sp_d = convops._splits((M + 127) // 128, (cin + (63 if cin <= 64 else 127)) // (64 if cin <= 64 else 128), TAPS * cout)
+                sp_w = convops._splits((cout + 127) // 128, (TAPS * cin + 127) // 128, M)
+                for nm, fn in (("forward", lambda: convops._tc_conv(1, x, w, yo, bias, B, H, H, cin, cout, sp_f, terms)),
+                               ("dgrad", lambda: convops._tc_conv(2, dyc, w, dxo, None, B, H, H, cin, cout, sp_d, terms)),
+                               ("wgrad", lambda: convops._tc_conv(3, x, dyc, dwo, None, B, H, H, cin, cout, sp_w, terms, accumulate=True))):
+                    us = timed_graph(fn, args.reps)
+                    rows.append({"op": f"{tag} gemm {nm} terms={terms}", "us": round(us, 2), "tflops": round(flop / us / 1e6, 1)})
+                    print(f"{tag + ' gemm ' + nm + f' terms={terms}':44s} {us:8.2f} us   {flop / us / 1e6:7.1f} TFLOP/s (algorithmic)", flush=True)
+
         def bn_fwd():
             _lib.check(lib.dl_bn_relu_pool_fwd(y.data_ptr(), p.data_ptr(), gamma.data_ptr(), beta.data_ptr(), mean.data_ptr(),
                                                invstd.data_ptr(), None, None, B, H, H, cout, 1e-3, 0.1, work.data_ptr(), st()))
