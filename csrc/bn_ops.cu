@@ -80,6 +80,8 @@ __device__ __forceinline__ double fin_sum(const float* partial, int nblocks, lon
   return t;
 }
 
+__global__ void colsum_finalize_kernel(const float* partial, int nblocks, int C, float* out, int accumulate);
+
 // mean / invstd from the sums; running statistics like nn.BatchNorm2d (momentum, unbiased variance)
 __global__ void bn_finalize_kernel(const float* partial, int nblocks, long long M, int C, float eps, float momentum,
                                    float* mean, float* invstd, float* running_mean, float* running_var) {
@@ -235,7 +237,13 @@ __global__ void __launch_bounds__(BN_THREADS) bn_relu_pool_bwd_apply_kernel(cons
                                                                             const float* __restrict__ beta,
                                                                             const float* __restrict__ mean,
                                                                             const float* __restrict__ invstd, int B, int H, int W,
-                                                                            int C4, const double* sum_dz, const double* sum_dzx) {
+                                                                            int C4, const double* sum_dz, const double* sum_dzx,
+                                                                            float4* __restrict__ colpart) {
+  // colpart != NULL: also leave the per-block column sums of dy (the bias gradient of the convolution in front of this
+  // block: dy IS the gradient of its output) so that nobody has to read dy again for them.  The grid stride is a multiple
+  // of C4 (256 % C4 == 0), so a thread keeps its channel group for the whole loop and sums in registers.
+  extern __shared__ float4 sh_col[];
+  float4 csum = make_float4(0.f, 0.f, 0.f, 0.f);
   const int Ho = H / 2, Wo = W / 2;
   const long long windows = static_cast<long long>(B) * Ho * Wo;
   const double invM = 1.0 / (static_cast<double>(windows) * 4.0);
@@ -277,8 +285,23 @@ __global__ void __launch_bounds__(BN_THREADS) bn_relu_pool_bwd_apply_kernel(cons
       }
     }
 #pragma unroll
-    for (int k = 0; k < 4; ++k)
+    for (int k = 0; k < 4; ++k) {
       dy[base + (static_cast<long long>(k >> 1) * W + (k & 1)) * C4] = make_float4(out[k][0], out[k][1], out[k][2], out[k][3]);
+      csum.x += out[k][0]; csum.y += out[k][1]; csum.z += out[k][2]; csum.w += out[k][3];
+    }
+  }
+  if (colpart != nullptr) {
+    sh_col[threadIdx.x] = csum;
+    __syncthreads();
+    if (threadIdx.x < C4) {
+      const int rows_per_pass = BN_THREADS / C4;
+      float4 ds = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int k = 0; k < rows_per_pass; ++k) {
+        const float4 a = sh_col[k * C4 + threadIdx.x];
+        ds.x += a.x; ds.y += a.y; ds.z += a.z; ds.w += a.w;
+      }
+      colpart[static_cast<long long>(blockIdx.x) * C4 + threadIdx.x] = ds;
+    }
   }
 }
 
@@ -298,7 +321,8 @@ static int bn_reduce_grid(long long rows, int rows_per_pass) {
 
 // scratch: per-block partial sums (float) followed by 2*C doubles
 extern "C" size_t dl_bn_work_bytes(int C) {
-  return static_cast<size_t>(BN_MAX_REDUCE_BLOCKS) * 2 * C * sizeof(float) + static_cast<size_t>(C) * 2 * sizeof(double);
+  // reduction partials (2 rows per block) + 2 C doubles + the column-sum partials of the fused conv-bias gradient
+  return static_cast<size_t>(BN_MAX_REDUCE_BLOCKS) * 3 * C * sizeof(float) + static_cast<size_t>(C) * 2 * sizeof(double);
 }
 
 // y [B,H,W,C] -> p [B,H/2,W/2,C]; writes mean/invstd [C] (saved for backward) and updates the running statistics.
@@ -336,6 +360,14 @@ extern "C" int dl_bn_relu_pool_fwd(const float* y, float* p, const float* gamma,
 extern "C" int dl_bn_relu_pool_bwd(const float* y, const float* dp, float* dy, const float* gamma, const float* beta,
                                    const float* mean, const float* invstd, float* dgamma, float* dbeta, int B, int H, int W, int C,
                                    int accumulate, void* work, void* stream) {
+  return dl_bn_relu_pool_bwd_bias(y, dp, dy, gamma, beta, mean, invstd, dgamma, dbeta, nullptr, B, H, W, C, accumulate, work, stream);
+}
+
+// Same, and with dconvbias != NULL the column sums of dy — the bias gradient of the convolution that produced y — come
+// out of the same pass (added into dconvbias when accumulate != 0), instead of a separate dl_colsum over dy.
+extern "C" int dl_bn_relu_pool_bwd_bias(const float* y, const float* dp, float* dy, const float* gamma, const float* beta,
+                                        const float* mean, const float* invstd, float* dgamma, float* dbeta, float* dconvbias, int B,
+                                        int H, int W, int C, int accumulate, void* work, void* stream) {
   DL_REQUIRE(y && dp && dy && gamma && beta && mean && invstd && dgamma && dbeta && work, "dl_bn_relu_pool_bwd: null pointer");
   DL_REQUIRE(C % 4 == 0 && C / 4 <= BN_THREADS && H % 2 == 0 && W % 2 == 0, "dl_bn_relu_pool_bwd: need C %% 4 == 0, C <= %d, even H and W",
              BN_THREADS * 4);
@@ -355,11 +387,19 @@ extern "C" int dl_bn_relu_pool_bwd(const float* y, const float* dp, float* dy, c
   bn_bwd_finalize_kernel<<<(C + FIN_X - 1) / FIN_X, dim3(FIN_X, FIN_Y), 0, st>>>(partial, nb, C, sums, dgamma, dbeta, accumulate);
   dl_note_launch();
   DL_CUDA(cudaGetLastError());
-  bn_relu_pool_bwd_apply_kernel<<<bn_grid(windows * C4, BN_THREADS), BN_THREADS, 0, st>>>(
+  float* colpart = reinterpret_cast<float*>(sums + 2 * static_cast<size_t>(C));
+  int grid = bn_grid(windows * C4, BN_THREADS);
+  if (dconvbias != nullptr && grid > BN_MAX_REDUCE_BLOCKS) grid = BN_MAX_REDUCE_BLOCKS;    // one partial row per block
+  bn_relu_pool_bwd_apply_kernel<<<grid, BN_THREADS, dconvbias ? BN_THREADS * sizeof(float4) : 0, st>>>(
       reinterpret_cast<const float4*>(y), reinterpret_cast<const float4*>(dp), reinterpret_cast<float4*>(dy), gamma, beta, mean, invstd,
-      B, H, W, C4, sums, sums + C);
+      B, H, W, C4, sums, sums + C, dconvbias ? reinterpret_cast<float4*>(colpart) : nullptr);
   dl_note_launch();
   DL_CUDA(cudaGetLastError());
+  if (dconvbias != nullptr) {
+    colsum_finalize_kernel<<<(C + FIN_X - 1) / FIN_X, dim3(FIN_X, FIN_Y), 0, st>>>(colpart, grid, C, dconvbias, accumulate);
+    dl_note_launch();
+    DL_CUDA(cudaGetLastError());
+  }
   return DL_OK;
 }
 

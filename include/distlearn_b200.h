@@ -278,6 +278,11 @@ int dl_bn_relu_pool_fwd(const float* y, float* p, const float* gamma, const floa
 int dl_bn_relu_pool_bwd(const float* y, const float* dp, float* dy, const float* gamma, const float* beta, const float* mean,
                         const float* invstd, float* dgamma, float* dbeta, int B, int H, int W, int C, int accumulate,
                         void* work, void* stream);
+/* dl_bn_relu_pool_bwd that also produces the bias gradient of the convolution in front of the block (dconvbias[C] (+)=
+ * column sums of dy; NULL: skip) in the same pass over dy — examples/Model.lua:20-24: conv -> BN -> ReLU -> pool. */
+int dl_bn_relu_pool_bwd_bias(const float* y, const float* dp, float* dy, const float* gamma, const float* beta, const float* mean,
+                             const float* invstd, float* dgamma, float* dbeta, float* dconvbias, int B, int H, int W, int C,
+                             int accumulate, void* work, void* stream);
 /* out[C] (+)= column sums of x[M, C] (a convolution's bias gradient); work: dl_bn_work_bytes(C) bytes.
  * accumulate != 0 (here and in dl_bn_relu_pool_bwd for dgamma/dbeta) adds into the buffer: the autograd functions
  * pass the parameters' .grad views so that no separate gradient-accumulation kernel runs. */

@@ -46,3 +46,28 @@ def test_fused_bn_relu_pool_matches_float64(B, H, C):
     # eval mode uses the running statistics through the plain torch path
     mod.eval(); ref.eval()
     close(mod(y), F.max_pool2d(F.relu(ref(y.double().permute(0, 3, 1, 2))), 2, 2).permute(0, 2, 3, 1), 1e-5)
+
+
+@pytest.mark.parametrize("B,H,C", [(128, 16, 128), (16, 32, 64), (128, 4, 512)])
+def test_conv_bias_gradient_comes_out_of_the_bn_backward(B, H, C):
+    """dl_bn_relu_pool_bwd_bias: the column sums of dy (= bias gradient of the convolution in front) from the same pass."""
+    from torch_distlearn_b200.ops import FusedBNReLUPool
+    from torch_distlearn_b200.ops.bn import _BIAS_DONE
+    g = torch.Generator().manual_seed(C)
+    y = torch.randn(B, H, H, C, generator=g).to(DEV)
+    dp = torch.randn(B, H // 2, H // 2, C, generator=g).to(DEV)
+    conv_bias = torch.nn.Parameter(torch.zeros(C, device=DEV))
+    conv_bias.grad = torch.full((C,), 0.25, device=DEV)          # the kernel adds into the existing gradient
+    mod = FusedBNReLUPool(C).to(DEV)
+    mod.attach_conv_bias(conv_bias)
+    for p in mod.parameters():
+        p.grad = torch.zeros_like(p)                              # direct accumulation needs allocated gradients
+    y1 = y.clone().requires_grad_(True)
+    mod(y1).backward(dp)
+    torch.cuda.synchronize()
+    assert id(conv_bias) in _BIAS_DONE
+    _BIAS_DONE.discard(id(conv_bias))
+    want = y1.grad.double().sum((0, 1, 2)) + 0.25
+    # the true value is ~0 (a bias in front of a BatchNorm has no gradient): compare on the scale of the summands
+    scale = float(y1.grad.abs().sum((0, 1, 2)).max())
+    assert float((conv_bias.grad.double() - want).abs().max()) < 1e-5 * scale + 1e-6

@@ -144,6 +144,7 @@ def cuda():
     _sig(lib, "dl_bn_work_bytes", sz, [i32])
     _sig(lib, "dl_bn_relu_pool_fwd", i32, [vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, f32, f32, vp, vp])
     _sig(lib, "dl_bn_relu_pool_bwd", i32, [vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp, vp])
+    _sig(lib, "dl_bn_relu_pool_bwd_bias", i32, [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp, vp])
     _sig(lib, "dl_colsum", i32, [vp, vp, C.c_longlong, i32, i32, vp, vp])
     _sig(lib, "dl_head_fwd", i32, [vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, vp])
     _sig(lib, "dl_head_bwd", i32, [vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp])

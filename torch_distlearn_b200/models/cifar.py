@@ -59,6 +59,9 @@ class CifarConvNetTC(nn.Module):
         self.bns = nn.ModuleList([FusedBNReLUPool(c, eps=1e-3) if fused_tail else nn.BatchNorm2d(c, eps=1e-3)
                                   for c in self.CHANNELS[1:]])
         self.linear = nn.Linear(512 * 2 * 2, 10)
+        if fused_tail:
+            for conv, bn in zip(self.convs, self.bns):
+                bn.attach_conv_bias(conv.bias)                     # bias gradient out of the block's own backward pass
 
     def execution_order(self):
         return _execution_order(self)

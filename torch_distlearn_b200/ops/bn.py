@@ -42,6 +42,18 @@ def grad_done(p) -> None:
 
 DIRECT_GRAD = True
 
+# Bias parameters whose gradient was already produced by the BatchNorm block behind their convolution (the column sums of
+# dy come out of the block's backward pass for free); the convolution's backward finds its bias here and skips its own
+# reduction over dy.  Filled and emptied within one backward pass.
+_BIAS_DONE = set()
+
+
+def take_bias_done(p) -> bool:
+    if id(p) in _BIAS_DONE:
+        _BIAS_DONE.discard(id(p))
+        return True
+    return False
+
 
 def colsum(x: torch.Tensor, out: "torch.Tensor | None" = None) -> "torch.Tensor | None":
     """Column sums of a contiguous [M, C] fp32 CUDA matrix (C % 4 == 0): the bias gradient of a convolution.
@@ -63,7 +75,8 @@ def colsum(x: torch.Tensor, out: "torch.Tensor | None" = None) -> "torch.Tensor 
 
 class _BNReLUPool(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, y, gamma, beta, running_mean, running_var, eps, momentum):
+    def forward(ctx, y, gamma, beta, running_mean, running_var, eps, momentum, conv_bias=None):
+        ctx.conv_bias = conv_bias
         y = y.contiguous()
         B, H, W, C = y.shape
         p = torch.empty(B, H // 2, W // 2, C, dtype=torch.float32, device=y.device)
@@ -91,15 +104,21 @@ class _BNReLUPool(torch.autograd.Function):
         dgamma = sink_g if direct else torch.empty(C, dtype=torch.float32, device=y.device)
         dbeta = sink_b if direct else torch.empty(C, dtype=torch.float32, device=y.device)
         work = torch.empty(int(_lib.cuda().dl_bn_work_bytes(C)) // 8 + 1, dtype=torch.float64, device=y.device)
+        # the convolution's bias gradient = column sums of dy: produced here, in the pass that writes dy, when the bias can
+        # take it directly (same conditions as for our own parameters)
+        sink_cb = grad_sink(ctx.conv_bias) if (direct and ctx.conv_bias is not None and ctx.conv_bias.requires_grad) else None
         with torch.cuda.device(y.device):
-            _lib.check(_lib.cuda().dl_bn_relu_pool_bwd(
+            _lib.check(_lib.cuda().dl_bn_relu_pool_bwd_bias(
                 y.data_ptr(), dp.data_ptr(), dy.data_ptr(), gamma.data_ptr(), beta.data_ptr(), mean.data_ptr(), invstd.data_ptr(),
-                dgamma.data_ptr(), dbeta.data_ptr(), B, H, W, C, int(direct), work.data_ptr(), _stream(y)))
+                dgamma.data_ptr(), dbeta.data_ptr(), sink_cb.data_ptr() if sink_cb is not None else None, B, H, W, C, int(direct),
+                work.data_ptr(), _stream(y)))
+        if sink_cb is not None:
+            _BIAS_DONE.add(id(ctx.conv_bias))
         if direct:
             grad_done(ctx.params[0])
             grad_done(ctx.params[1])
-            return dy, None, None, None, None, None, None
-        return dy, dgamma, dbeta, None, None, None, None
+            return dy, None, None, None, None, None, None, None
+        return dy, dgamma, dbeta, None, None, None, None, None
 
 
 class FusedBNReLUPool(torch.nn.Module):
@@ -114,12 +133,20 @@ class FusedBNReLUPool(torch.nn.Module):
         self.register_buffer("running_mean", torch.zeros(channels))
         self.register_buffer("running_var", torch.ones(channels))
         self.register_buffer("num_batches_tracked", torch.tensor(0, dtype=torch.long))
+        self._conv_bias = None
+
+    def attach_conv_bias(self, bias: torch.nn.Parameter) -> None:
+        """``bias`` belongs to the convolution whose output this block normalises: its gradient (the column sums of the
+        gradient this block's backward produces) is then computed inside that backward pass instead of by a separate
+        reduction in the convolution's backward.  Not a module attribute on purpose: the parameter stays the convolution's."""
+        object.__setattr__(self, "_conv_bias", bias)
 
     def forward(self, y: torch.Tensor) -> torch.Tensor:
         if self.training and y.is_cuda:
             # (num_batches_tracked is not advanced: it only matters for momentum=None, and a host-side
             # counter update would be one more tiny kernel per layer per step)
-            return _BNReLUPool.apply(y, self.weight, self.bias, self.running_mean, self.running_var, self.eps, self.momentum)
+            return _BNReLUPool.apply(y, self.weight, self.bias, self.running_mean, self.running_var, self.eps, self.momentum,
+                                     self._conv_bias)
         z = F.batch_norm(y.permute(0, 3, 1, 2), self.running_mean, self.running_var, self.weight, self.bias, self.training,
                          self.momentum, self.eps)
         return F.max_pool2d(F.relu(z), 2, 2).permute(0, 2, 3, 1)

@@ -126,8 +126,12 @@ class _Conv5x5Implicit(torch.autograd.Function):
             else:
                 dw = torch.empty(cout, kc, dtype=torch.float32, device=x.device)
                 _tc_conv(3, x, dy, dw, None, B, H, W, C, cout, _splits((cout + 127) // 128, (kc + 127) // 128, M), terms)
+        bias_done = False
         if has_bias and ctx.needs_input_grad[2]:
-            db = colsum(dy.view(M, cout), out=grad_sink(ctx.params[1]))
+            from .bn import take_bias_done
+            bias_done = take_bias_done(ctx.params[1])      # the BatchNorm block behind us already added it into bias.grad
+            if not bias_done:
+                db = colsum(dy.view(M, cout), out=grad_sink(ctx.params[1]))
         if ctx.needs_input_grad[0]:
             bn = 64 if C <= 64 else 128
             dx = torch.empty(B, H, W, C, dtype=torch.float32, device=x.device)
@@ -172,9 +176,12 @@ class _Conv5x5(torch.autograd.Function):
             dw_full = tc_gemm(dy2, col, a_mn=True, b_mn=True, terms=terms,
                               split_k=_splits((cout + 127) // 128, (ld + bn - 1) // bn, M))
             dw = dw_full[:, :kc] if ld != kc else dw_full
+        bias_done = False
         if has_bias and ctx.needs_input_grad[2]:
-            from .bn import colsum, grad_done, grad_sink
-            db = colsum(dy2, out=grad_sink(ctx.params[1]))
+            from .bn import colsum, grad_done, grad_sink, take_bias_done
+            bias_done = take_bias_done(ctx.params[1])
+            if not bias_done:
+                db = colsum(dy2, out=grad_sink(ctx.params[1]))
         if ctx.needs_input_grad[0]:
             dcol = tc_gemm(dy2, w, b_mn=True, terms=terms)          # [M, ld]; K = Cout is short, no split
             dx = col2im5x5(dcol, (B, H, W, C))
