@@ -69,7 +69,11 @@ def parse():
                         "(0 = one launch after backward; default: 0.5 for N > 1 = one bucket per layer of this model)")
     p.add_argument("--bucket-blocks", type=int, default=0,
                    help="CTAs per bucket launch (0 = one light CTA per SM, beside the convolution's CTA)")
+    p.add_argument("--nvls-permille", type=int, default=-1,
+                   help="share of every slice the hybrid / light kernels reduce in the switch (-1: the measured table's value)")
     a = p.parse_args()
+    if a.nvls_permille >= 0:
+        os.environ["DL_B200_NVLS_PERMILLE"] = str(a.nvls_permille)
     if a.graph is None:
         a.graph = 1 if a.impl == "ours" else 0
     return a

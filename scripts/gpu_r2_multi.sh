@@ -18,11 +18,12 @@ grep "variant table" gpurun_out/r2_sweep_${N}_graph.log | cut -c1-400
 python scripts/merge_variant_table.py gpurun_out/variant_table_${N}_graph.json $N; echo "table merge rc=$?"
 b() { name=$1; shift; timeout 200 $TR --master-port 29551 bench.py --gpus $N --steps 100 --warmup 10 "$@" > gpurun_out/r2_bench${N}_$name.log 2>&1; echo "bench $name rc=$? $(tail -n 1 gpurun_out/r2_bench${N}_$name.log | cut -c1-160)"; }
 b b0 --baselines 0 --bucket-mb 0
-b mod05 --baselines 0 --bucket-mb 0.5 --flat-order module
 b exe05 --baselines 0 --bucket-mb 0.5 --flat-order execution
-b exe05_b16 --baselines 0 --bucket-mb 0.5 --flat-order execution --bucket-blocks 16
-b exe05_b64 --baselines 0 --bucket-mb 0.5 --flat-order execution --bucket-blocks 64
+b exe05_b32 --baselines 0 --bucket-mb 0.5 --flat-order execution --bucket-blocks 32
+b exe05_b74 --baselines 0 --bucket-mb 0.5 --flat-order execution --bucket-blocks 74
 b exe2 --baselines 0 --bucket-mb 2 --flat-order execution
+b exe05_p0 --baselines 0 --bucket-mb 0.5 --flat-order execution --nvls-permille 0
+b exe05_p1000 --baselines 0 --bucket-mb 0.5 --flat-order execution --nvls-permille 1000
 b default
 b gb32 --global-batch 32
 b ea --algo ea
