@@ -25,7 +25,8 @@
 #include "dl_common.cuh"
 
 #define DL_PIPE_THREADS 256
-#define DL_PIPE_MC_U 4  // multimem.ld_reduce vectors per thread per stage (2 stages in flight)
+#define DL_PIPE_MC_U 8  // multimem.ld_reduce vectors per thread per stage (2 stages in flight): the switch round trip is long —
+                        // with 4 the 8-GPU all-switch pass moved 528 GB/s per direction where the two phases alone do 715-725
 
 struct DlPipeRange {
   unsigned long long r0, r1;  // slice-relative range of this block in float4 units (both even)
@@ -214,7 +215,7 @@ __device__ __forceinline__ void dl_pipe_foreach_released(unsigned long long n4, 
 // per source in flight per thread and no double buffering — the bytes in flight come from running on ALL SMs at once
 // (148 x 128 threads x 8 sources x 16 B = 2.4 MB, the bandwidth-delay product of the links).
 #define DL_LIGHT_THREADS 128
-#define DL_LIGHT_MC_U 4
+#define DL_LIGHT_MC_U 8
 
 template <int W, typename Epi>
 __device__ __forceinline__ void dl_light_p2p(const dl_comm_t& c, int world, uint32_t lmask, uint64_t src_off, uint64_t dst_off,

@@ -189,18 +189,37 @@ __global__ void __launch_bounds__(DL_THREADS) ll_kernel(dl_comm_t c, LlArgs a) {
     const unsigned long long idx = tid0 + u * stride;
     if (!ok || idx >= a.nvec) continue;
     uint4 v[DL_MAX_RANKS];
+    // Every source's two packets are requested before the first flag is looked at: the 2 x (N-1) loads are independent, so
+    // a round of polling costs ONE trip to the L2 instead of 14 in a row (8 GPUs: that chain alone was ~8 us, which is why
+    // the push path lost to the barrier kernels above 4 KiB in the first 8-GPU sweep).  Sources that have not arrived yet
+    // are asked again, all of them together.
+    uint32_t pending = srcmask & ~(1u << rank) & ((1u << world) - 1u);
+    unsigned long long t0 = 0;
+    unsigned int polls = 0;
 #pragma unroll
-    for (int j = 0; j < DL_MAX_RANKS; ++j) {
-      v[j] = make_uint4(0u, 0u, 0u, 0u);
-      if (j < world && ((srcmask >> j) & 1u)) {
-        if (j == rank) {
-          v[j] = own[u];
-        } else {
+    for (int j = 0; j < DL_MAX_RANKS; ++j)      // (unrolled, static indices: v stays in registers)
+      v[j] = (j == rank && ((srcmask >> j) & 1u)) ? own[u] : make_uint4(0u, 0u, 0u, 0u);
+    while (pending != 0u) {
+      uint4 p0[DL_MAX_RANKS], p1[DL_MAX_RANKS];
+#pragma unroll
+      for (int j = 0; j < DL_MAX_RANKS; ++j) {
+        if ((pending >> j) & 1u) {
           const uint4* slot = ll_slot(c, rank, a.channel, parity, j) + 1 + 2 * idx;
-          uint4 p0, p1;
-          ok = ok && ll_wait(slot, flag, limit, &p0) && ll_wait(slot + 1, flag, limit, &p1);
-          v[j] = make_uint4(p0.x, p0.z, p1.x, p1.z);
+          p0[j] = dl_ll_load(slot);
+          p1[j] = dl_ll_load(slot + 1);
         }
+      }
+#pragma unroll
+      for (int j = 0; j < DL_MAX_RANKS; ++j) {
+        if (((pending >> j) & 1u) && p0[j].y == flag && p0[j].w == flag && p1[j].y == flag && p1[j].w == flag) {
+          v[j] = make_uint4(p0[j].x, p0[j].z, p1[j].x, p1[j].z);
+          pending &= ~(1u << j);
+        }
+      }
+      if (pending != 0u && (++polls & 255u) == 0u) {
+        const unsigned long long now = dl_globaltimer();
+        if (t0 == 0) t0 = now;
+        if (now - t0 > limit) { ok = false; break; }
       }
     }
     if (!ok) break;
