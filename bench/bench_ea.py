@@ -36,6 +36,9 @@ def main():
     ap.add_argument("--alpha", type=float, default=0.2)
     ap.add_argument("--lr", type=float, default=0.01)
     ap.add_argument("--fused", type=int, default=1, help="ours: the one-kernel MNIST step (batch <= 8)")
+    ap.add_argument("--graph-steps", type=int, default=0,
+                    help="local steps per CUDA-graph replay (0 = tau): the tau steps between two exchanges are one replay, "
+                         "each step reading its own batch in place, so the host issues 2 launches per tau steps in both arms")
     args = ap.parse_args()
     rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
     local = int(os.environ.get("LOCAL_RANK", rank))
@@ -77,11 +80,12 @@ def main():
         mp, mg = model_tensors(model)
         loss_dev = torch.zeros(1, device=dev)
 
-    def local_step():
+    def local_step(xb=None, yb=None):
+        xb, yb = (x, y) if xb is None else (xb, yb)
         if fused:
-            mnist_step(x, y, mp, mg, loss_dev, None, lr=args.lr, apply_sgd=True)       # examples/mnist-ea.lua:100-107 in one launch
+            mnist_step(xb, yb, mp, mg, loss_dev, None, lr=args.lr, apply_sgd=True)     # examples/mnist-ea.lua:100-107 in one launch
             return
-        F.nll_loss(model(x), y).backward()
+        F.nll_loss(model(xb), yb).backward()
         local_sgd(p, gr, None, lr=args.lr, zero_grads=True)
 
     side = torch.cuda.Stream()
@@ -91,15 +95,17 @@ def main():
             local_step()
     torch.cuda.current_stream().wait_stream(side)
     torch.cuda.synchronize()
+    G = args.graph_steps or args.tau
+    assert args.tau % G == 0 and G <= 16, "--graph-steps must divide tau and be at most 16"
     graph = torch.cuda.CUDAGraph()
     with torch.cuda.graph(graph):
-        local_step()
+        for k in range(G):
+            local_step(xs[k], ys[k])          # every step of the replay trains on its own batch, read in place
 
     def step(i):
-        x.copy_(xs[i % 16], non_blocking=True)
-        y.copy_(ys[i % 16], non_blocking=True)
-        graph.replay()
-        exchange()
+        if i % G == 0:
+            graph.replay()
+        exchange()                            # counts the step; every tau-th call launches the exchange
 
     for i in range(args.warmup):
         step(i)
@@ -115,7 +121,7 @@ def main():
     ms = max_over_ranks(e0.elapsed_time(e1), world)
     if rank == 0:
         print(json.dumps({"bench": "mnist_allreduce_ea", "impl": args.impl, "fused_local_step": bool(fused), "n_gpus": world,
-                          "per_gpu_batch": B, "tau": args.tau,
+                          "per_gpu_batch": B, "tau": args.tau, "steps_per_graph_replay": G,
                           "alpha": args.alpha, "steps": args.steps, "ms_per_step": round(ms / args.steps, 5),
                           "samples_per_s": round(B * world * args.steps / (ms / 1e3), 1),
                           "exchanges_per_s": round(args.steps / args.tau / (ms / 1e3), 1)}))
