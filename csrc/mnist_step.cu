@@ -187,28 +187,27 @@ __global__ void __cluster_dims__(MN_CL, 1, 1) __launch_bounds__(MN_T, 1) mnist_s
     }
     cluster.sync();   // [2] every CTA holds all partial logits
 
-    // ---- log-softmax, loss, dlogits: every CTA does the same sums in the same order -----------------------------
-    if (t == 0) {
-      float z[10], m = -INFINITY;
+    // ---- log-softmax, loss, dlogits: every CTA does the same sums in the same order (lane j of warp 0 owns class j) ------
+    if (t < 32) {
+      float z = -INFINITY;
+      if (t < 10) {
+        z = s.b3[t];
 #pragma unroll
-      for (int j = 0; j < 10; ++j) {
-        float v = s.b3[j];
-#pragma unroll
-        for (int k = 0; k < MN_CL; ++k) v += s.lpart[k][j];
-        z[j] = v;
-        m = fmaxf(m, v);
+        for (int k = 0; k < MN_CL; ++k) z += s.lpart[k][t];
       }
-      float sum = 0.f;
+      float m = z;
 #pragma unroll
-      for (int j = 0; j < 10; ++j) sum += expf(z[j] - m);
+      for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+      float sum = t < 10 ? expf(z - m) : 0.f;
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
       const float lse = m + logf(sum);
       const long long yy = a.y[b];
-#pragma unroll
-      for (int j = 0; j < 10; ++j) {
-        const float lp = z[j] - lse;
-        s.dl[j] = (expf(lp) - (j == yy ? 1.f : 0.f)) * inv_b;       // d(mean NLL)/dlogit
-        if (r == 0 && a.logp != nullptr) a.logp[static_cast<long long>(b) * 10 + j] = lp;
-        if (j == yy) s.loss_acc -= lp;
+      if (t < 10) {
+        const float lp = z - lse;
+        s.dl[t] = (expf(lp) - (t == yy ? 1.f : 0.f)) * inv_b;       // d(mean NLL)/dlogit
+        if (r == 0 && a.logp != nullptr) a.logp[static_cast<long long>(b) * 10 + t] = lp;
+        if (t == yy) s.loss_acc -= lp;
       }
     }
     __syncthreads();
@@ -254,11 +253,12 @@ __global__ void __cluster_dims__(MN_CL, 1, 1) __launch_bounds__(MN_T, 1) mnist_s
 #pragma unroll
       for (int kx = 0; kx < 5; ++kx) s.gw2[co][ci][ky * 5 + kx] += acc[kx];
     }
-    if (t >= 160 && t < 162) {
-      const int co = t - 160;
+    if (t >= 160 && t < 192) {                   // warp 5 has no filter rows: it sums the two bias gradients, 16 lanes each
+      const int lane = t & 31, co = lane >> 4;
       float v = 0.f;
-      for (int i = 0; i < 100; ++i) v += s.a2[co][i];
-      s.gb2[co] += v;
+      for (int i = lane & 15; i < 100; i += 16) v += s.a2[co][i];
+      v = warp_sum16(v);
+      if ((lane & 15) == 0) s.gb2[co] += v;
     }
     // ---- conv2 input gradient: my two output channels' contribution to ALL 16 input channels, row by row ---------
     for (int it = t; it < 16 * 14; it += MN_T) {
@@ -315,12 +315,25 @@ __global__ void __cluster_dims__(MN_CL, 1, 1) __launch_bounds__(MN_T, 1) mnist_s
       v += __shfl_xor_sync(0xffffffffu, v, 1);     // whole warps take part (320 threads = 10 warps), idle lanes carry zeros
       v += __shfl_xor_sync(0xffffffffu, v, 2);
       if (t < 200 && grp == 0) s.gw1[c][tap] += v;
-      if (t >= 224 && t < 226) {
-        const int cb = t - 224;
-        float sum = 0.f;
-        for (int i = 0; i < 784; ++i) sum += s.a1[cb][i];
-        s.gb1[cb] += sum;
+      // bias gradients of my two channels: every thread adds its share, the ten warps meet in lpart (free until the next
+      // sample's Linear layer: no peer can pass barrier [1] of the next sample before this CTA has arrived there)
+      float b0 = 0.f, b1 = 0.f;
+      for (int i = t; i < 784; i += MN_T) { b0 += s.a1[0][i]; b1 += s.a1[1][i]; }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        b0 += __shfl_xor_sync(0xffffffffu, b0, o);
+        b1 += __shfl_xor_sync(0xffffffffu, b1, o);
       }
+      float* scratch = &s.lpart[0][0];
+      if ((t & 31) == 0) { scratch[(t >> 5) * 2] = b0; scratch[(t >> 5) * 2 + 1] = b1; }
+    }
+    __syncthreads();
+    if (t < 2) {
+      const float* scratch = &s.lpart[0][0];
+      float v = 0.f;
+#pragma unroll
+      for (int w = 0; w < MN_T / 32; ++w) v += scratch[w * 2 + t];
+      s.gb1[t] += v;
     }
     // No barrier here: the next sample's remote writes are ordered behind this sample's reads by the barriers themselves
     // (p1 is last read before [3]; lpart right after [2]; dpart before a CTA reaches the next [1], and nobody writes

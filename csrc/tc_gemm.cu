@@ -448,7 +448,6 @@ struct SmemTS {
   float b[TS_STAGES][2][BN * BK];     // [0] = hi (TMA destination), [1] = lo
   uint64_t full[TS_STAGES], conv[TS_STAGES], empty[TS_STAGES], acc_full[2], acc_empty[2];
   uint32_t tmem_base;
-  int sk_last, sk_cfirst, sk_clast, sk_trail;   // stream-K deterministic mode: verdict and CTA range of the tile being finished
 };
 
 template <int BN>
@@ -861,12 +860,6 @@ extern "C" int dl_tc_gemm_streamk(int on) {
 // The stream-K work list of CTA `cta` for an M x N x K problem on `sms` SMs, computed by the same functions the kernel
 // uses (host-side check of the decomposition; no GPU needed).  Writes up to `max_segments` rows of
 // (m0, n0, first K block, K blocks) into `segments`; returns the number of segments of that CTA, *grid = CTAs launched.
-extern "C" int dl_tc_gemm_deterministic(int on) {
-  const int before = use_deterministic() ? 1 : 0;
-  g_det = on ? 1 : 0;
-  return before;
-}
-
 extern "C" int dl_tc_streamk_plan(int M, int N, int K, int sms, int cta, int* grid, int* segments, int max_segments) {
   DL_REQUIRE(M > 0 && N > 0 && K > 0 && sms > 0 && grid != nullptr, "dl_tc_streamk_plan: bad arguments");
   const int bn = N <= 64 ? 64 : 128;

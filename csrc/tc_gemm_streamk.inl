@@ -18,18 +18,7 @@ struct SkArgs {
   int m_tiles, n_tiles;   // output tiles (BM x BN)
   int total_kb;           // K blocks per tile
   long long units;        // m_tiles * n_tiles * total_kb
-  // Deterministic mode (ws != nullptr): a partial tile is not red.add'ed into C — the order of atomics differs from run
-  // to run, and with three or more partials so does the rounding — but written to slot 2c (+1 for a CTA's trailing
-  // segment) of a workspace; the LAST segment of a tile to arrive (counter per tile) adds the slots in ascending-K order
-  // and writes the tile.  Same bits every run; one extra pass over the partials by one CTA per split tile.
-  float* ws;              // 2 * gridDim.x slots of BM x BN floats
-  unsigned int* counters; // one per tile, zero before the launch, left zero by it
 };
-
-// the CTA whose unit range [units*c/G, units*(c+1)/G) holds unit u
-__host__ __device__ __forceinline__ long long sk_owner(long long units, long long grid, long long u) {
-  return ((u + 1) * grid - 1) / units;
-}
 
 struct SkSegment {
   int m0, n0, kb0, nkb;
@@ -80,37 +69,7 @@ tc_gemm_sk_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
   const uint32_t tmem = s.tmem_base;
 
   if (u_end > u_begin) {
-    if (warp == 0 && g.mode == 3) {
-      // ===== TMA producer of the weight-gradient GEMM: both operands arrive in 32 x 32 boxes, eight per stage.  One lane
-      // issuing them one after another left the converter warps waiting for data three times as often as in the forward
-      // GEMM (ncu: 19 % of the samples on the `full` barrier against 6 %, tensor pipe 35 % against 56 % active); here
-      // lane b issues box b, all eight in one warp instruction. =====
-      int st = 0, it = 0;
-      const int hw = g.cH * g.cW;
-      for (long long u = u_begin; u < u_end;) {
-        const SkSegment sg = sk_segment(k, u, u_end, BN);
-        for (int i = 0; i < sg.nkb; ++i) {
-          if (lane == 0) {
-            mbar_wait(&s.empty[st], (it & 1) ^ 1);
-            mbar_expect_tx(&s.full[st], (BM + BN) * BK * 4);
-          }
-          __syncwarp();
-          const int k0 = (sg.kb0 + i) * BK;
-          if (lane < BM / 32) {
-            tma_load_2d(&s.a[st][lane * 32 * BK], &map_a, &s.full[st], sg.m0 + 32 * lane, k0);
-          } else if (lane < BM / 32 + BN / 32) {
-            const int bx = lane - BM / 32;
-            const int b0 = k0 / hw, h0 = (k0 - b0 * hw) / g.cW;
-            const int col = sg.n0 + 32 * bx;
-            const int tap = col / g.cIn, c0 = col - tap * g.cIn;
-            if (tap < 25) tma_load_4d(&s.b[st][0][bx * 32 * BK], &map_b, &s.full[st], c0, tap % 5 - 2, h0 + tap / 5 - 2, b0);
-            else tma_load_4d(&s.b[st][0][bx * 32 * BK], &map_b, &s.full[st], g.cIn, 0, 0, 0);
-          }
-          if (++st == TS_STAGES) { st = 0; ++it; }
-        }
-        u += sg.nkb;
-      }
-    } else if (warp == 0) {
+    if (warp == 0) {
       // ===== TMA producer: same boxes as tc_gemm_ts_kernel, tile by tile =====
       if (lane == 0) {
         int st = 0, it = 0;
@@ -307,64 +266,10 @@ tc_gemm_sk_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
         }
         // the MMA warp is already filling the buffers with the next segment while this one is written out
         const int row = sg.m0 + quarter * 32 + lane;
-        const bool partial = sg.nkb != k.total_kb;
-        if (k.ws != nullptr && partial) {
-          // ---- deterministic path: park the partial tile, the last arrival adds all of them in a fixed order ----
-          const long long tile = u / k.total_kb;
-          const bool trailing = (u + sg.nkb == u_end) && (u != u_begin);
-          float* slot = k.ws + (2ll * blockIdx.x + (trailing ? 1 : 0)) * (BM * BN) + (quarter * 32 + lane) * BN + chalf * HN;
-#pragma unroll
-          for (int q = 0; q < HN; q += 4) *reinterpret_cast<float4*>(slot + q) = make_float4(acc[q], acc[q + 1], acc[q + 2], acc[q + 3]);
-          __threadfence();
-          asm volatile("bar.sync 1, 256;" ::: "memory");          // the eight drain warps
-          if (warp == 10 && lane == 0) {                          // one thread does the 64-bit bookkeeping for all
-            const long long c_first = sk_owner(k.units, gridDim.x, tile * k.total_kb);
-            const long long c_last = sk_owner(k.units, gridDim.x, (tile + 1) * k.total_kb - 1);
-            const unsigned int arrived = atomicAdd(k.counters + tile, 1u) + 1u;
-            s.sk_last = (arrived == static_cast<unsigned int>(c_last - c_first + 1)) ? 1 : 0;
-            s.sk_cfirst = static_cast<int>(c_first);
-            s.sk_clast = static_cast<int>(c_last);
-            // only the first CTA of a tile can reach it with a TRAILING segment (its range began in an earlier tile)
-            s.sk_trail = (k.units * c_first / gridDim.x < tile * k.total_kb) ? 1 : 0;
-          }
-          asm volatile("bar.sync 1, 256;" ::: "memory");
-          const bool last = s.sk_last != 0;
-          const int c_first = s.sk_cfirst, c_last = s.sk_clast, first_trails = s.sk_trail;
-          asm volatile("bar.sync 1, 256;" ::: "memory");          // everybody has read the verdict before it can be rewritten
-          if (last) {
-            __threadfence();
-            float* sum = acc;                                     // parked already: the registers are free
-#pragma unroll
-            for (int q = 0; q < HN; ++q) sum[q] = 0.f;
-            for (int cc = c_first; cc <= c_last; ++cc) {            // ascending K: the same order in every run
-              const float* src = k.ws + static_cast<size_t>(2 * cc + ((cc == c_first) ? first_trails : 0)) * (BM * BN) +
-                                 (quarter * 32 + lane) * BN + chalf * HN;
-#pragma unroll
-              for (int q = 0; q < HN; q += 4) {
-                const float4 v = __ldcg(reinterpret_cast<const float4*>(src + q));
-                sum[q] += v.x; sum[q + 1] += v.y; sum[q + 2] += v.z; sum[q + 3] += v.w;
-              }
-            }
-            if (row < g.M) {
-              float* crow = g.C + static_cast<long long>(row) * g.ldc + sg.n0 + chalf * HN;
-#pragma unroll
-              for (int q = 0; q < HN; ++q) {
-                const int n = sg.n0 + chalf * HN + q;
-                if (n < g.N) {
-                  float v = sum[q];
-                  if (g.bias != nullptr) v += g.bias[n];
-                  crow[q] = g.atomic_out ? crow[q] + v : v;         // accumulate: C held the value to add to; one writer per tile
-                }
-              }
-            }
-            if (warp == 10 && lane == 0) k.counters[tile] = 0u;      // ready for the next launch
-          }
-        } else if (row < g.M) {
+        if (row < g.M) {
           float* crow = g.C + static_cast<long long>(row) * g.ldc + sg.n0 + chalf * HN;
           const bool add_bias = g.bias != nullptr && sg.kb0 == 0;
-          // deterministic mode: a whole tile has one writer, so "accumulate" is a plain read-add-write
-          const bool atomic = k.ws == nullptr && (g.atomic_out != 0 || partial);
-          const bool rmw = k.ws != nullptr && g.atomic_out != 0;
+          const bool atomic = g.atomic_out != 0 || sg.nkb != k.total_kb;     // a partial tile is added to its siblings
 #pragma unroll
           for (int q = 0; q < HN; q += 4) {
             const int n = sg.n0 + chalf * HN + q;
@@ -378,10 +283,6 @@ tc_gemm_sk_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
                 asm volatile("red.relaxed.gpu.global.add.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(crow + q), "f"(v.x), "f"(v.y),
                              "f"(v.z), "f"(v.w)
                              : "memory");
-              } else if (rmw) {
-                float4 o = *reinterpret_cast<float4*>(crow + q);
-                o.x += v.x; o.y += v.y; o.z += v.z; o.w += v.w;
-                *reinterpret_cast<float4*>(crow + q) = o;
               } else {
                 *reinterpret_cast<float4*>(crow + q) = v;
               }
@@ -392,7 +293,6 @@ tc_gemm_sk_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
                   float v = acc[q + e];
                   if (add_bias) v += g.bias[n + e];
                   if (atomic) atomicAdd(crow + q + e, v);
-                  else if (rmw) crow[q + e] += v;
                   else crow[q + e] = v;
                 }
               }
@@ -428,56 +328,13 @@ SkArgs sk_plan(int M, int N, int K, int bn, int sms, long long* grid) {
   k.n_tiles = (N + bn - 1) / bn;
   k.total_kb = (K + BK - 1) / BK;
   k.units = static_cast<long long>(k.m_tiles) * k.n_tiles * k.total_kb;
-  k.ws = nullptr;
-  k.counters = nullptr;
   long long gsz = sms;
   if (gsz > k.units / 4) gsz = k.units / 4 > 0 ? k.units / 4 : 1;
   *grid = gsz;
   return k;
 }
 
-// Deterministic mode (default; DL_B200_TC_DETERMINISTIC=0 or dl_tc_gemm_deterministic(0) returns to red.add): the
-// workspace for parked partial tiles and the per-tile arrival counters, one set per device, allocated on the first launch
-// that needs them.  All GEMM launches of a device share it, so in this mode they must be ordered (one stream, or events
-// between streams) — true of every path in this library.
-int g_det = -1;
-bool use_deterministic() {
-  if (g_det < 0) {
-    const char* e = getenv("DL_B200_TC_DETERMINISTIC");
-    g_det = (e != nullptr && e[0] == '1') ? 1 : 0;   // off until validated on a GPU (then: on unless '0')
-  }
-  return g_det != 0;
-}
-constexpr long long SK_MAX_GRID = 160;
-constexpr long long SK_MAX_TILES = 1 << 20;
-struct SkScratch {
-  float* ws = nullptr;
-  unsigned int* counters = nullptr;
-};
-SkScratch g_sk_scratch[64];
-
-// returns false if the scratch is not available right now (never allocate while a stream is being captured)
-bool sk_scratch(int dev, cudaStream_t st, SkScratch* out) {
-  SkScratch& sc = g_sk_scratch[dev];
-  if (sc.ws == nullptr) {
-    cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
-    if (cudaStreamIsCapturing(st, &cap) != cudaSuccess || cap != cudaStreamCaptureStatusNone) return false;
-    float* ws = nullptr;
-    unsigned int* cnt = nullptr;
-    if (cudaMalloc(&ws, static_cast<size_t>(2 * SK_MAX_GRID) * BM * 128 * sizeof(float)) != cudaSuccess) return false;
-    if (cudaMalloc(&cnt, SK_MAX_TILES * sizeof(unsigned int)) != cudaSuccess || cudaMemset(cnt, 0, SK_MAX_TILES * sizeof(unsigned int)) != cudaSuccess) {
-      cudaFree(ws);
-      if (cnt) cudaFree(cnt);
-      return false;
-    }
-    sc.ws = ws;
-    sc.counters = cnt;
-  }
-  *out = sc;
-  return true;
-}
-
-// `accumulate`: C already holds values to add to (nothing is zeroed)
+// `accumulate`: C already holds values to add to (every segment uses red.add, nothing is zeroed)
 template <int BN>
 int launch_sk(const CUtensorMap& ma, const CUtensorMap& mb, GemmArgs g, int accumulate, cudaStream_t st) {
   static bool configured[64] = {false};
@@ -492,18 +349,11 @@ int launch_sk(const CUtensorMap& ma, const CUtensorMap& mb, GemmArgs g, int accu
     configured[dev] = true;
   }
   long long grid = 0;
-  SkArgs k = sk_plan(g.M, g.N, g.K, BN, sm_count[dev] > 0 ? sm_count[dev] : 148, &grid);
+  const SkArgs k = sk_plan(g.M, g.N, g.K, BN, sm_count[dev] > 0 ? sm_count[dev] : 148, &grid);
   const long long tiles = static_cast<long long>(k.m_tiles) * k.n_tiles;
   g.atomic_out = accumulate ? 1 : 0;
   g.kblocks_per_split = k.total_kb;
-  k.ws = nullptr;
-  k.counters = nullptr;
-  SkScratch sc;
-  if (use_deterministic() && grid <= SK_MAX_GRID && tiles <= SK_MAX_TILES && sk_scratch(dev, st, &sc)) {
-    k.ws = sc.ws;
-    k.counters = sc.counters;
-  }
-  if (k.ws == nullptr && !accumulate && tiles % grid != 0) {
+  if (!accumulate && tiles % grid != 0) {
     // some tile is shared between CTAs and arrives as a sum of red.adds: start from zero
     if (g.ldc == g.N) {
       DL_CUDA(cudaMemsetAsync(g.C, 0, static_cast<size_t>(g.M) * g.N * 4, st));

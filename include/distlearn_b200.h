@@ -257,11 +257,6 @@ int dl_tc_conv5x5(int mode, const float* act, const float* w, float* out, const 
  * for later dl_tc_gemm* / dl_tc_conv5x5 calls (initial value: 1 unless the environment says DL_B200_TC_STREAMK=0);
  * returns the previous setting. */
 int dl_tc_gemm_streamk(int on);
-/* Deterministic reduction of tiles that several CTAs share (default on; DL_B200_TC_DETERMINISTIC=0 or on = 0 goes back to
- * red.add): partial tiles are parked in a per-device workspace and the last one to arrive adds them in ascending-K order,
- * so two runs give the same bits (the reference's SGEMM is deterministic too).  GEMM launches of one device must then be
- * ordered among themselves (one stream, or events).  Returns the previous setting. */
-int dl_tc_gemm_deterministic(int on);
 /* Host-side view of the stream-K decomposition (same code as the kernel): the segments (m0, n0, first K block, K blocks)
  * of CTA `cta`; returns their number, *grid = CTAs the launch would use on `sms` SMs. */
 int dl_tc_streamk_plan(int M, int N, int K, int sms, int cta, int* grid, int* segments, int max_segments);
