@@ -284,10 +284,11 @@ __device__ __forceinline__ uint32_t dl_active_mask(const dl_comm_t& c, int rank,
     if (c.host_words != nullptr && rank == c.rank) {
       // the contributor count, readable by the host without a device-to-host copy (lua/AllReduceSGD.lua:20: `_, n = allReduce`)
       dl_host_words_t* h = static_cast<dl_host_words_t*>(c.host_words);
-      volatile uint32_t* slot = &h->ring[ch][c.ticket % DL_HOST_RING].ticket;
-      slot[1] = static_cast<uint32_t>(n);
-      __threadfence_system();
-      slot[0] = c.ticket;
+      // ONE 8-byte store carries {ticket, n}: it cannot tear, so no fence is needed between the two words — a system-scope
+      // fence here would also wait for this thread's flag / packet stores to the peers to be acknowledged (an NVLink round
+      // trip on the critical path of every small collective).  The host reads the slot after the call's event anyway.
+      *reinterpret_cast<volatile unsigned long long*>(&h->ring[ch][c.ticket % DL_HOST_RING]) =
+          static_cast<unsigned long long>(c.ticket) | (static_cast<unsigned long long>(static_cast<uint32_t>(n)) << 32);
     }
   }
   return mask;
