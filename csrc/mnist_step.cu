@@ -21,6 +21,7 @@
 // than one cluster (B > 8 or so) each takes every n-th sample and the gradients meet in global memory with atomics, the
 // update then being a separate dl_local_sgd.  With ONE cluster and apply_sgd != 0 the update is fused: one launch per step.
 #include <cooperative_groups.h>
+#include <cstdlib>
 
 #include "dl_common.cuh"
 #include "dl_host.h"
@@ -29,6 +30,7 @@ namespace cg = cooperative_groups;
 
 #define MN_CL 8      // CTAs per cluster: 2 of the 16 channels each
 #define MN_T 320     // threads per CTA = 2 output channels x 10 output rows x 16 input channels (conv2's natural shape)
+#define MN_T2 416    // second form: 13 warps — conv1 in one round (392 windows), conv2's two backward passes side by side (7 + 5 warps)
 
 struct MnistArgs {
   const float* x;            // [B, 1024]
@@ -69,7 +71,18 @@ __device__ __forceinline__ float warp_sum16(float v) {  // sum over the 16 lanes
   return v;
 }
 
-__global__ void __cluster_dims__(MN_CL, 1, 1) __launch_bounds__(MN_T, 1) mnist_step_kernel(MnistArgs a) {
+// kV2 = false: the first form (320 threads).  kV2 = true: the form written after its ncu capture
+// (profiles/ncu_tails_r2.md: 15 % of the issue slots used, 34 % of the samples in conv1's filter gradient, a single
+// chain of 196 dependent FMAs per thread on shared-memory reads that collide 6-fold):
+//   * conv1's filter gradient: warp = (channel, filter row), lane = output column — contiguous conflict-free reads,
+//     five independent sums per lane, the bias gradient falls out of the same loop;
+//   * conv2's weight gradient and input gradient on different warps (416 threads) instead of one after the other;
+//   * one tanh per thread after conv2 instead of ten under a predicate; the label is fetched at the top of the sample,
+//     not inside the softmax; the update reads the parameters from shared memory, where they already are.
+// Same sums up to the order of the additions inside conv1's filter gradient.
+template <bool kV2>
+__global__ void __cluster_dims__(MN_CL, 1, 1) __launch_bounds__(kV2 ? MN_T2 : MN_T, 1) mnist_step_kernel(MnistArgs a) {
+  constexpr int T = kV2 ? MN_T2 : MN_T;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   MnistSmem& s = *reinterpret_cast<MnistSmem*>(smem_raw);
   cg::cluster_group cluster = cg::this_cluster();
@@ -82,17 +95,17 @@ __global__ void __cluster_dims__(MN_CL, 1, 1) __launch_bounds__(MN_T, 1) mnist_s
   for (int k = 0; k < MN_CL; ++k) peer[k] = cluster.map_shared_rank(&s, k);
 
   // ---- parameters of my channels into shared memory, gradient accumulators to zero ---------------------------
-  for (int i = t; i < 50; i += MN_T) (&s.w1[0][0])[i] = a.p[0][(2 * r) * 25 + i];
-  for (int i = t; i < 800; i += MN_T) (&s.w2[0][0][0])[i] = a.p[2][(2 * r) * 400 + i];
-  for (int i = t; i < 500; i += MN_T) {
+  for (int i = t; i < 50; i += T) (&s.w1[0][0])[i] = a.p[0][(2 * r) * 25 + i];
+  for (int i = t; i < 800; i += T) (&s.w2[0][0][0])[i] = a.p[2][(2 * r) * 400 + i];
+  for (int i = t; i < 500; i += T) {
     const int j = i / 50, f = i - j * 50;
     s.w3[j][f] = a.p[4][j * 400 + 2 * r * 25 + f];
   }
   if (t < 2) { s.b1[t] = a.p[1][2 * r + t]; s.b2[t] = a.p[3][2 * r + t]; }
   if (t < 10) s.b3[t] = a.p[5][t];
-  for (int i = t; i < 50; i += MN_T) (&s.gw1[0][0])[i] = 0.f;
-  for (int i = t; i < 800; i += MN_T) (&s.gw2[0][0][0])[i] = 0.f;
-  for (int i = t; i < 500; i += MN_T) (&s.gw3[0][0])[i] = 0.f;
+  for (int i = t; i < 50; i += T) (&s.gw1[0][0])[i] = 0.f;
+  for (int i = t; i < 800; i += T) (&s.gw2[0][0][0])[i] = 0.f;
+  for (int i = t; i < 500; i += T) (&s.gw3[0][0])[i] = 0.f;
   if (t < 2) { s.gb1[t] = 0.f; s.gb2[t] = 0.f; }
   if (t < 10) s.gb3[t] = 0.f;
   if (t == 0) s.loss_acc = 0.f;
@@ -102,11 +115,13 @@ __global__ void __cluster_dims__(MN_CL, 1, 1) __launch_bounds__(MN_T, 1) mnist_s
   for (int b = cid; b < a.B; b += ncl) {
     // ---- input -------------------------------------------------------------------------------------------------
     const float4* xin = reinterpret_cast<const float4*>(a.x + static_cast<long long>(b) * 1024);
-    for (int i = t; i < 256; i += MN_T) reinterpret_cast<float4*>(s.x)[i] = xin[i];
+    long long y_early = 0;
+    if (kV2 && t < 32) y_early = a.y[b];      // in flight while the convolutions run
+    for (int i = t; i < 256; i += T) reinterpret_cast<float4*>(s.x)[i] = xin[i];
     __syncthreads();
 
     // ---- conv1 + tanh + 2x2 max-pool for my two channels: one item = one pooling window -----------------------------
-    for (int it = t; it < 2 * 196; it += MN_T) {
+    for (int it = t; it < 2 * 196; it += T) {
       const int c = it / 196, pos = it - c * 196, py = pos / 14, px = pos - py * 14;
       float in[6][6];
 #pragma unroll
@@ -139,7 +154,7 @@ __global__ void __cluster_dims__(MN_CL, 1, 1) __launch_bounds__(MN_T, 1) mnist_s
     cluster.sync();   // [1] every CTA holds all 16 pooled maps
 
     // ---- conv2 + tanh for my two output channels: thread = (co, output row, input channel) -------------------------
-    {
+    if (!kV2 || t < MN_T) {   // (whole warps: 320 = 10 x 32)
       const int ci = t & 15, oy = (t >> 4) % 10, co = t / 160;
       float acc[10];
 #pragma unroll
@@ -156,10 +171,20 @@ __global__ void __cluster_dims__(MN_CL, 1, 1) __launch_bounds__(MN_T, 1) mnist_s
           for (int ox = 0; ox < 10; ++ox) acc[ox] = fmaf(w, row[ox + kx], acc[ox]);
         }
       }
+      if (kV2) {
+        float mine = 0.f;
 #pragma unroll
-      for (int ox = 0; ox < 10; ++ox) {
-        const float v = warp_sum16(acc[ox]);      // over the 16 input channels, fixed butterfly order
-        if (ci == 0) s.a2[co][oy * 10 + ox] = tanhf(v + s.b2[co]);
+        for (int ox = 0; ox < 10; ++ox) {
+          const float v = warp_sum16(acc[ox]);    // every lane of the half warp ends up with the sum
+          if (ci == ox) mine = v;
+        }
+        if (ci < 10) s.a2[co][oy * 10 + ci] = tanhf(mine + s.b2[co]);
+      } else {
+#pragma unroll
+        for (int ox = 0; ox < 10; ++ox) {
+          const float v = warp_sum16(acc[ox]);      // over the 16 input channels, fixed butterfly order
+          if (ci == 0) s.a2[co][oy * 10 + ox] = tanhf(v + s.b2[co]);
+        }
       }
     }
     __syncthreads();
@@ -177,7 +202,7 @@ __global__ void __cluster_dims__(MN_CL, 1, 1) __launch_bounds__(MN_T, 1) mnist_s
     }
     __syncthreads();
     // ---- Linear: warp j forms my 50-feature part of logit j and hands it to every CTA ----------------------------
-    {
+    if (!kV2 || t < MN_T) {
       const int j = t >> 5, lane = t & 31;
       const float* f = &s.p2[0][0];
       float v = s.w3[j][lane] * f[lane] + (lane < 18 ? s.w3[j][32 + lane] * f[32 + lane] : 0.f);
@@ -202,7 +227,7 @@ __global__ void __cluster_dims__(MN_CL, 1, 1) __launch_bounds__(MN_T, 1) mnist_s
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
       const float lse = m + logf(sum);
-      const long long yy = a.y[b];
+      const long long yy = kV2 ? y_early : a.y[b];
       if (t < 10) {
         const float lp = z - lse;
         s.dl[t] = (expf(lp) - (t == yy ? 1.f : 0.f)) * inv_b;       // d(mean NLL)/dlogit
@@ -213,7 +238,7 @@ __global__ void __cluster_dims__(MN_CL, 1, 1) __launch_bounds__(MN_T, 1) mnist_s
     __syncthreads();
 
     // ---- Linear backward for my 50 features; un-pool and tanh' into conv2's pre-activation gradient ----------------
-    for (int i = t; i < 500; i += MN_T) {
+    for (int i = t; i < 500; i += T) {
       const int j = i / 50, f = i - j * 50;
       s.gw3[j][f] = fmaf(s.dl[j], (&s.p2[0][0])[f], s.gw3[j][f]);
     }
@@ -236,7 +261,7 @@ __global__ void __cluster_dims__(MN_CL, 1, 1) __launch_bounds__(MN_T, 1) mnist_s
     __syncthreads();
 
     // ---- conv2 weight / bias gradients: thread = (co, ci, filter row), five taps each ---------------------------------
-    for (int it = t; it < 2 * 16 * 5; it += MN_T) {
+    for (int it = kV2 ? t - 224 : t; it >= 0 && it < 2 * 16 * 5; it += T) {   // (second form: warps 7..11, beside the input gradient)
       const int co = it / 80, rem = it - co * 80, ci = rem / 5, ky = rem - ci * 5;
       float acc[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
       for (int oy = 0; oy < 10; ++oy) {
@@ -253,7 +278,7 @@ __global__ void __cluster_dims__(MN_CL, 1, 1) __launch_bounds__(MN_T, 1) mnist_s
 #pragma unroll
       for (int kx = 0; kx < 5; ++kx) s.gw2[co][ci][ky * 5 + kx] += acc[kx];
     }
-    if (t >= 160 && t < 192) {                   // warp 5 has no filter rows: it sums the two bias gradients, 16 lanes each
+    if (kV2 ? t < 32 : (t >= 160 && t < 192)) {  // first form: warp 5 has no filter rows; it sums the two bias gradients, 16 lanes each
       const int lane = t & 31, co = lane >> 4;
       float v = 0.f;
       for (int i = lane & 15; i < 100; i += 16) v += s.a2[co][i];
@@ -261,7 +286,7 @@ __global__ void __cluster_dims__(MN_CL, 1, 1) __launch_bounds__(MN_T, 1) mnist_s
       if ((lane & 15) == 0) s.gb2[co] += v;
     }
     // ---- conv2 input gradient: my two output channels' contribution to ALL 16 input channels, row by row ---------
-    for (int it = t; it < 16 * 14; it += MN_T) {
+    for (int it = t; it < 16 * 14; it += T) {
       const int ci = it / 14, yy = it - ci * 14;
       float acc[14];
 #pragma unroll
@@ -290,7 +315,7 @@ __global__ void __cluster_dims__(MN_CL, 1, 1) __launch_bounds__(MN_T, 1) mnist_s
     cluster.sync();   // [3] my eight slots are filled
 
     // ---- conv1 backward for my two channels: sum the slots, un-pool, tanh', then the filter gradients ----------------
-    for (int it = t; it < 2 * 196; it += MN_T) {
+    for (int it = t; it < 2 * 196; it += T) {
       const int c = it / 196, pos = it - c * 196, py = pos / 14, px = pos - py * 14;
       float dp = 0.f;
 #pragma unroll
@@ -303,37 +328,70 @@ __global__ void __cluster_dims__(MN_CL, 1, 1) __launch_bounds__(MN_T, 1) mnist_s
       }
     }
     __syncthreads();
-    // thread = (channel, filter tap, one of 4 row groups); the groups meet in fixed order through shared scratch (lpart
-    // and dfeat are free by now)
-    {
-      const int c = (t / 100) & 1, rem = t % 100, tap = rem >> 2, grp = rem & 3, ky = tap / 5, kx = tap - ky * 5;
-      float v = 0.f;
-      if (t < 200) {
-        for (int oy = grp * 7; oy < grp * 7 + 7; ++oy)
-          for (int ox = 0; ox < 28; ++ox) v = fmaf(s.a1[c][oy * 28 + ox], s.x[(oy + ky) * 32 + ox + kx], v);
-      }
-      v += __shfl_xor_sync(0xffffffffu, v, 1);     // whole warps take part (320 threads = 10 warps), idle lanes carry zeros
-      v += __shfl_xor_sync(0xffffffffu, v, 2);
-      if (t < 200 && grp == 0) s.gw1[c][tap] += v;
-      // bias gradients of my two channels: every thread adds its share, the ten warps meet in lpart (free until the next
-      // sample's Linear layer: no peer can pass barrier [1] of the next sample before this CTA has arrived there)
-      float b0 = 0.f, b1 = 0.f;
-      for (int i = t; i < 784; i += MN_T) { b0 += s.a1[0][i]; b1 += s.a1[1][i]; }
+    if (kV2) {
+      // warp = (channel, filter row ky), lane = output column: lane ox adds d[oy][ox] * x[oy+ky][ox+kx] over the 28 rows into
+      // five sums (one per kx) — both reads walk consecutive words across the lanes — then the lanes meet by butterfly.  The
+      // bias gradient (sum of d) rides along in the two ky == 0 warps.
+      const int w = t >> 5, lane = t & 31;
+      if (w < 10) {
+        const int c = w / 5, ky = w - c * 5;
+        float acc[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
+        float bs = 0.f;
+        if (lane < 28) {
+#pragma unroll 4
+          for (int oy = 0; oy < 28; ++oy) {
+            const float d = s.a1[c][oy * 28 + lane];
+            const float* xr = &s.x[(oy + ky) * 32 + lane];
 #pragma unroll
-      for (int o = 16; o > 0; o >>= 1) {
-        b0 += __shfl_xor_sync(0xffffffffu, b0, o);
-        b1 += __shfl_xor_sync(0xffffffffu, b1, o);
-      }
-      float* scratch = &s.lpart[0][0];
-      if ((t & 31) == 0) { scratch[(t >> 5) * 2] = b0; scratch[(t >> 5) * 2 + 1] = b1; }
-    }
-    __syncthreads();
-    if (t < 2) {
-      const float* scratch = &s.lpart[0][0];
-      float v = 0.f;
+            for (int kx = 0; kx < 5; ++kx) acc[kx] = fmaf(d, xr[kx], acc[kx]);
+            bs += d;
+          }
+        }
 #pragma unroll
-      for (int w = 0; w < MN_T / 32; ++w) v += scratch[w * 2 + t];
-      s.gb1[t] += v;
+        for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+          for (int kx = 0; kx < 5; ++kx) acc[kx] += __shfl_xor_sync(0xffffffffu, acc[kx], o);
+          bs += __shfl_xor_sync(0xffffffffu, bs, o);
+        }
+        if (lane == 0) {
+#pragma unroll
+          for (int kx = 0; kx < 5; ++kx) s.gw1[c][ky * 5 + kx] += acc[kx];
+          if (ky == 0) s.gb1[c] += bs;
+        }
+      }
+    } else {
+      // thread = (channel, filter tap, one of 4 row groups); the groups meet in fixed order through shared scratch (lpart
+      // and dfeat are free by now)
+      {
+        const int c = (t / 100) & 1, rem = t % 100, tap = rem >> 2, grp = rem & 3, ky = tap / 5, kx = tap - ky * 5;
+        float v = 0.f;
+        if (t < 200) {
+          for (int oy = grp * 7; oy < grp * 7 + 7; ++oy)
+            for (int ox = 0; ox < 28; ++ox) v = fmaf(s.a1[c][oy * 28 + ox], s.x[(oy + ky) * 32 + ox + kx], v);
+        }
+        v += __shfl_xor_sync(0xffffffffu, v, 1);     // whole warps take part (320 threads = 10 warps), idle lanes carry zeros
+        v += __shfl_xor_sync(0xffffffffu, v, 2);
+        if (t < 200 && grp == 0) s.gw1[c][tap] += v;
+        // bias gradients of my two channels: every thread adds its share, the ten warps meet in lpart (free until the next
+        // sample's Linear layer: no peer can pass barrier [1] of the next sample before this CTA has arrived there)
+        float b0 = 0.f, b1 = 0.f;
+        for (int i = t; i < 784; i += T) { b0 += s.a1[0][i]; b1 += s.a1[1][i]; }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+          b0 += __shfl_xor_sync(0xffffffffu, b0, o);
+          b1 += __shfl_xor_sync(0xffffffffu, b1, o);
+        }
+        float* scratch = &s.lpart[0][0];
+        if ((t & 31) == 0) { scratch[(t >> 5) * 2] = b0; scratch[(t >> 5) * 2 + 1] = b1; }
+      }
+      __syncthreads();
+      if (t < 2) {
+        const float* scratch = &s.lpart[0][0];
+        float v = 0.f;
+#pragma unroll
+        for (int w = 0; w < MN_T / 32; ++w) v += scratch[w * 2 + t];
+        s.gb1[t] += v;
+      }
     }
     // No barrier here: the next sample's remote writes are ordered behind this sample's reads by the barriers themselves
     // (p1 is last read before [3]; lpart right after [2]; dpart before a CTA reaches the next [1], and nobody writes
@@ -344,31 +402,44 @@ __global__ void __cluster_dims__(MN_CL, 1, 1) __launch_bounds__(MN_T, 1) mnist_s
   // ---- gradients out (or the update itself) ----------------------------------------------------------------------
   __syncthreads();
   const bool fused = a.apply_sgd != 0 && ncl == 1;
-  auto emit = [&](float* p, float* g, float grad) {
+  auto emit = [&](float* p, float* g, float grad, float mine) {   // `mine`: this CTA's shared-memory copy of *p
     if (fused) {
-      *p = fmaf(-a.lr, grad, *p);        // same rounding as the flat-vector SGD kernels (csrc/fused_sgd.cu)
+      *p = fmaf(-a.lr, grad, kV2 ? mine : *p);   // same rounding as the flat-vector SGD kernels (csrc/fused_sgd.cu)
     } else if (ncl == 1) {
       *g += grad;                        // accumulate into .grad like autograd would
     } else {
       atomicAdd(g, grad);
     }
   };
-  for (int i = t; i < 50; i += MN_T) emit(a.p[0] + 2 * r * 25 + i, a.g[0] + 2 * r * 25 + i, (&s.gw1[0][0])[i]);
-  for (int i = t; i < 800; i += MN_T) emit(a.p[2] + 2 * r * 400 + i, a.g[2] + 2 * r * 400 + i, (&s.gw2[0][0][0])[i]);
-  for (int i = t; i < 500; i += MN_T) {
+  for (int i = t; i < 50; i += T) emit(a.p[0] + 2 * r * 25 + i, a.g[0] + 2 * r * 25 + i, (&s.gw1[0][0])[i], (&s.w1[0][0])[i]);
+  for (int i = t; i < 800; i += T) emit(a.p[2] + 2 * r * 400 + i, a.g[2] + 2 * r * 400 + i, (&s.gw2[0][0][0])[i], (&s.w2[0][0][0])[i]);
+  for (int i = t; i < 500; i += T) {
     const int j = i / 50, f = i - j * 50, at = j * 400 + 2 * r * 25 + f;
-    emit(a.p[4] + at, a.g[4] + at, s.gw3[j][f]);
+    emit(a.p[4] + at, a.g[4] + at, s.gw3[j][f], s.w3[j][f]);
   }
   if (t < 2) {
-    emit(a.p[1] + 2 * r + t, a.g[1] + 2 * r + t, s.gb1[t]);
-    emit(a.p[3] + 2 * r + t, a.g[3] + 2 * r + t, s.gb2[t]);
+    emit(a.p[1] + 2 * r + t, a.g[1] + 2 * r + t, s.gb1[t], s.b1[t]);
+    emit(a.p[3] + 2 * r + t, a.g[3] + 2 * r + t, s.gb2[t], s.b2[t]);
   }
-  if (r == 0 && t < 10) emit(a.p[5] + t, a.g[5] + t, s.gb3[t]);
+  if (r == 0 && t < 10) emit(a.p[5] + t, a.g[5] + t, s.gb3[t], s.b3[t]);
   if (r == 0 && t == 0) {
     if (ncl == 1) *a.loss = s.loss_acc * inv_b;
     else atomicAdd(a.loss, s.loss_acc * inv_b);
   }
   cluster.sync();   // no CTA may leave while a peer could still touch its shared memory
+}
+
+// Which form of the kernel runs: 2 (default) or 1 — DL_B200_MNIST_FORM at load time, dl_mnist_form() afterwards (returns
+// the previous value; anything but 1 or 2 only reads it).
+static int mnist_form_from_env() {
+  const char* e = getenv("DL_B200_MNIST_FORM");
+  return (e != nullptr && e[0] == '1') ? 1 : 2;
+}
+static int g_mnist_form = mnist_form_from_env();
+extern "C" int dl_mnist_form(int form) {
+  const int before = g_mnist_form;
+  if (form == 1 || form == 2) g_mnist_form = form;
+  return before;
 }
 
 // x [B,1024] fp32, y [B] int64; params / grads: the six tensors of the model in module order.  apply_sgd != 0 (and a
@@ -393,11 +464,13 @@ extern "C" int dl_mnist_step(const float* x, const int64_t* y, float* const* par
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   static bool configured = false;
   if (!configured) {
-    DL_CUDA(cudaFuncSetAttribute(mnist_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(sizeof(MnistSmem))));
+    DL_CUDA(cudaFuncSetAttribute(mnist_step_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(sizeof(MnistSmem))));
+    DL_CUDA(cudaFuncSetAttribute(mnist_step_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(sizeof(MnistSmem))));
     configured = true;
   }
   if (ncl > 1) DL_CUDA(cudaMemsetAsync(loss, 0, sizeof(float), st));
-  mnist_step_kernel<<<ncl * MN_CL, MN_T, sizeof(MnistSmem), st>>>(a);
+  if (g_mnist_form == 1) mnist_step_kernel<false><<<ncl * MN_CL, MN_T, sizeof(MnistSmem), st>>>(a);
+  else mnist_step_kernel<true><<<ncl * MN_CL, MN_T2, sizeof(MnistSmem), st>>>(a);
   dl_note_launch();
   DL_CUDA(cudaGetLastError());
   return DL_OK;

@@ -40,6 +40,7 @@ def main(argv=None):
                                 and torch.cuda.device_count() >= opt.numNodes) else "dist"
     comm, log = setup(opt)
     dev = comm.device
+    print(f"node {opt.nodeIndex} of {opt.numNodes}: backend {comm.backend}, device {dev}", flush=True)   # every node, not only the logger's
     batch = math.ceil(opt.batchSize / opt.numNodes)
     data = Data(opt.nodeIndex, opt.numNodes, batch, device=dev, train_samples=opt.trainSamples, test_samples=opt.testSamples,
                 native=not opt.pythonLoader, threads=opt.loaderThreads)

@@ -306,6 +306,9 @@ int dl_head_bwd(const float* feat, const float* w, const float* logp, const int6
 #define DL_MNIST_FUSED_MAX_BATCH 8
 int dl_mnist_step(const float* x, const int64_t* y, float* const* params, float* const* grads, float* loss, float* logp, int B,
                   float lr, int apply_sgd, void* stream);
+/* Which form of the one-launch MNIST kernel runs: 2 (default: 416 threads, csrc/mnist_step.cu) or 1 (the first form, kept as
+ * the reference for it); returns the previous value, any other argument only reads it.  DL_B200_MNIST_FORM=1 sets it at load. */
+int dl_mnist_form(int form);
 
 /* ---- local flat-vector ops (single GPU, no communication) ---- */
 /* p -= lr * (g*scale [+ wd*p] [momentum]); optionally zero g. world==1 fast path. */

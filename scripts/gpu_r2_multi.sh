@@ -37,5 +37,5 @@ done
 for impl in ours nccl; do
 timeout 120 $TR --master-port 29546 bench/bench_ea.py --impl $impl --batch 1 --steps 2000 > gpurun_out/${P}_mnist_ea${N}_$impl.log 2>&1; echo "mnist ea $impl rc=$? $(tail -n 1 gpurun_out/${P}_mnist_ea${N}_$impl.log | cut -c1-300)"
 done
-[ "$MODE" = "full" ] && timeout 120 $TR --master-port 29546 bench/bench_ea.py --impl ours --fused 0 --batch 1 --steps 2000 > gpurun_out/${P}_mnist_ea${N}_ours_unfused.log 2>&1; echo "mnist ea ours unfused rc=$? $(tail -n 1 gpurun_out/${P}_mnist_ea${N}_ours_unfused.log | cut -c1-300)"
+if [ "$MODE" = "full" ]; then timeout 120 $TR --master-port 29546 bench/bench_ea.py --impl ours --fused 0 --batch 1 --steps 2000 > gpurun_out/${P}_mnist_ea${N}_ours_unfused.log 2>&1; echo "mnist ea ours unfused rc=$? $(tail -n 1 gpurun_out/${P}_mnist_ea${N}_ours_unfused.log | cut -c1-300)"; fi
 echo "total $(( $(date +%s) - t0 ))s"

@@ -151,6 +151,7 @@ def cuda():
     _sig(lib, "dl_im2col5x5", i32, [vp, vp, i32, i32, i32, i32, C.c_longlong, vp])
     _sig(lib, "dl_col2im5x5", i32, [vp, vp, i32, i32, i32, i32, C.c_longlong, vp])
     _sig(lib, "dl_mnist_step", i32, [vp, vp, P(vp), P(vp), vp, vp, i32, f32, i32, vp])
+    _sig(lib, "dl_mnist_form", i32, [i32])
     _sig(lib, "dl_local_sgd", i32, [vp, vp, vp, u64, f32, f32, f32, i32, f32, i32, vp])
     _sig(lib, "dl_local_sgd_from", i32, [vp, vp, vp, vp, u64, f32, f32, f32, i32, f32, i32, vp])
     _sig(lib, "dl_async_ea_client_out", i32, [cp, i32, vp, vp, u64, u64, f32, i32, i32, vp])
