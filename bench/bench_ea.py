@@ -24,6 +24,7 @@ sys.path.insert(0, ROOT)
 import torch
 import torch.distributed as dist
 import torch.nn.functional as F
+from torch_distlearn_b200 import _lib  # noqa: E402
 
 
 def main():
@@ -120,7 +121,7 @@ def main():
     torch.cuda.synchronize()
     ms = max_over_ranks(e0.elapsed_time(e1), world)
     if rank == 0:
-        print(json.dumps({"bench": "mnist_allreduce_ea", "impl": args.impl, "fused_local_step": bool(fused), "n_gpus": world,
+        print(json.dumps({"bench": "mnist_allreduce_ea", "impl": args.impl, "fused_local_step": bool(fused), "mnist_kernel_form": (int(_lib.cuda().dl_mnist_form(0)) if fused else None), "n_gpus": world,
                           "per_gpu_batch": B, "tau": args.tau, "steps_per_graph_replay": G,
                           "alpha": args.alpha, "steps": args.steps, "ms_per_step": round(ms / args.steps, 5),
                           "samples_per_s": round(B * world * args.steps / (ms / 1e3), 1),

@@ -10,6 +10,15 @@ pytestmark = pytest.mark.gpu
 DEV = "cuda:0"
 
 
+@pytest.fixture(autouse=True, params=[2, 1], ids=["form2", "form1"])
+def kernel_form(request):
+    """Every test runs on both forms of the kernel (csrc/mnist_step.cu: 416 threads, the default; and the first one)."""
+    from torch_distlearn_b200 import _lib
+    before = _lib.cuda().dl_mnist_form(request.param)
+    yield request.param
+    _lib.cuda().dl_mnist_form(before)
+
+
 def _reference(model, x, y):
     ref = copy.deepcopy(model).double().cpu()
     out = ref(x.double().cpu())
