@@ -49,7 +49,7 @@ struct MnistSmem {
   float w1[2][25], b1[2];
   float a1[2][28 * 28];        // tanh(conv1); overwritten by the gradient w.r.t. conv1's pre-activation in the backward pass
   unsigned char i1[2][196];    // arg-max position (0..3) inside each pooling window
-  float p1[16][196];           // pooled conv1 maps of ALL channels (gathered through DSMEM)
+  alignas(16) float p1[16][196];   // pooled conv1 maps of ALL channels (gathered through DSMEM)
   float w2[2][16][25], b2[2];
   float a2[2][100];            // tanh(conv2), later its pre-activation gradient
   unsigned char i2[2][25];
@@ -58,7 +58,8 @@ struct MnistSmem {
   float lpart[MN_CL][10];      // partial logits of every CTA (all-reduce slots)
   float dl[10];                // dlogits
   float dfeat[2][25];
-  float dpart[MN_CL][2][196];  // conv2 dgrad contributions for MY two channels, one slot per source CTA
+  float dpart[MN_CL][2][196];  // conv2 dgrad contributions for MY two channels, one slot per source CTA (second form: the
+                               // same words hold MY contributions to all 16 channels, [16][196], and the owners fetch them)
   float gw1[2][25], gb1[2], gw2[2][16][25], gb2[2], gw3[10][50], gb3[10];   // gradient accumulators over the batch
   float loss_acc;
 };
@@ -148,10 +149,24 @@ __global__ void __cluster_dims__(MN_CL, 1, 1) __launch_bounds__(kV2 ? MN_T2 : MN
         if (v > best) { best = v; arg = k; }      // first maximum in row-major order, like max_pool2d
       }
       s.i1[c][pos] = static_cast<unsigned char>(arg);
+      if (kV2) {
+        s.p1[2 * r + c][pos] = best;             // the peers fetch it after the barrier (below)
+      } else {
 #pragma unroll
-      for (int k = 0; k < MN_CL; ++k) peer[k]->p1[2 * r + c][pos] = best;   // all-gather through distributed shared memory
+        for (int k = 0; k < MN_CL; ++k) peer[k]->p1[2 * r + c][pos] = best;   // all-gather through distributed shared memory
+      }
     }
-    cluster.sync();   // [1] every CTA holds all 16 pooled maps
+    cluster.sync();   // [1] first form: every CTA holds all 16 pooled maps; second form: every CTA's two maps are final
+    if (kV2) {
+      // Pull instead of push: a barrier with remote stores in flight waits until the last of them has landed (ERRBAR, 20 % of the
+      // samples of the first capture of this form); remote LOADS are 16 bytes wide, issued back to back, and nothing waits
+      // for them but their user.  98 float4 per peer, 7 peers.
+      for (int i = t; i < (MN_CL - 1) * 98; i += T) {
+        const int k0 = i / 98, q = i - k0 * 98, k = k0 + (k0 >= r ? 1 : 0);
+        reinterpret_cast<float4*>(&s.p1[2 * k][0])[q] = reinterpret_cast<const float4*>(&peer[k]->p1[2 * k][0])[q];
+      }
+      __syncthreads();
+    }
 
     // ---- conv2 + tanh for my two output channels: thread = (co, output row, input channel) -------------------------
     if (!kV2 || t < MN_T) {   // (whole warps: 320 = 10 x 32)
@@ -308,18 +323,20 @@ __global__ void __cluster_dims__(MN_CL, 1, 1) __launch_bounds__(kV2 ? MN_T2 : MN
           }
         }
       }
-      float* dst = &peer[ci >> 1]->dpart[r][ci & 1][yy * 14];         // reduce-scatter: slot r of the channel's owner
+      // reduce-scatter: first form — into slot r of the channel's owner; second form — kept here, the owner fetches it
+      float* dst = kV2 ? &(&s.dpart[0][0][0])[ci * 196 + yy * 14] : &peer[ci >> 1]->dpart[r][ci & 1][yy * 14];
 #pragma unroll
       for (int xx = 0; xx < 14; ++xx) dst[xx] = acc[xx];
     }
-    cluster.sync();   // [3] my eight slots are filled
+    cluster.sync();   // [3] first form: my eight slots are filled; second form: every CTA's contributions are final
 
     // ---- conv1 backward for my two channels: sum the slots, un-pool, tanh', then the filter gradients ----------------
     for (int it = t; it < 2 * 196; it += T) {
       const int c = it / 196, pos = it - c * 196, py = pos / 14, px = pos - py * 14;
       float dp = 0.f;
 #pragma unroll
-      for (int k = 0; k < MN_CL; ++k) dp += s.dpart[k][c][pos];        // rank order
+      for (int k = 0; k < MN_CL; ++k)                                  // rank order in both forms: the same bits
+        dp += kV2 ? (&peer[k]->dpart[0][0][0])[(2 * r + c) * 196 + pos] : s.dpart[k][c][pos];
       const int arg = s.i1[c][pos];
 #pragma unroll
       for (int k = 0; k < 4; ++k) {

@@ -501,7 +501,7 @@ class _CudaOps(Communicator):
             # Beside the convolutions the switch path is the one that pays: a multimem load is one instruction per 16 bytes
             # of EIGHT ranks' data, where the P2P form spends eight loads and eight stores of the SMs it shares (8 GPUs,
             # per-layer buckets: 898k samples/s all-switch, 830k at 750/1000, 821k all-P2P, 879k without buckets).
-            self._c.nvls_permille = self._variants.light_permille if (self.has_multicast and self.world > 2) else 0
+            self._c.nvls_permille = self._variants.light_permille if (self.has_multicast and self.world != 2) else 0
         with torch.cuda.device(self.device), _Range(f"distlearn.fused_sgd[{VARIANT_TEXT[v]}]"):
             _lib.check(self._lib.dl_fused_sgd(C.byref(self._c), grads.offset, params.offset,
                                               momentum_buf.offset if momentum_buf else 0, n, lr, momentum, weight_decay,
@@ -634,7 +634,11 @@ class P2PCommunicator(_CudaOps):
     backend = "p2p"
 
     def __init__(self, rank: Optional[int] = None, world: Optional[int] = None, device: Optional[torch.device] = None,
-                 heap_mb: float = 256, mode: str = "auto", use_multicast: Optional[bool] = None, group=None):
+                 heap_mb: float = 256, mode: str = "auto", use_multicast: Optional[bool] = None, group=None,
+                 self_multicast: bool = False):
+        """``self_multicast`` (world 1 only): put the heap in VMM memory and bind it to a multicast object of ONE device,
+        so that the switch-reduction kernels (``multimem.ld_reduce`` / ``multimem.st``: the nvls, hybrid and light variants)
+        run on a single-GPU box — the driver's test machine.  Raises if the driver refuses such an object."""
         import torch.distributed as dist
         if world is None:
             world = dist.get_world_size(group) if dist.is_initialized() else 1
@@ -657,7 +661,13 @@ class P2PCommunicator(_CudaOps):
         torch.cuda.set_device(dev)
         if use_multicast is None:
             use_multicast = os.environ.get("DL_B200_DISABLE_NVLS", "0") != "1"
-        if world == 1:
+        if world == 1 and self_multicast:
+            self._bootstrap_vmm(True)
+            if not self.has_multicast:
+                err = getattr(self, "_mc_error", None) or "multicast is not supported on this device"
+                self.close()
+                raise RuntimeError(f"single-device multicast object refused: {err}")
+        elif world == 1:
             self._heap_tensor = torch.zeros(heap_bytes, dtype=torch.uint8, device=device)
             self._c.base[0] = self._heap_tensor.data_ptr()
             self._bytes = self._heap_tensor
@@ -676,6 +686,8 @@ class P2PCommunicator(_CudaOps):
             self._dist.barrier(group=self._group)
 
     def _all_gather_obj(self, obj):
+        if self.world == 1:
+            return [obj]
         out = [None] * self.world
         self._dist.all_gather_object(out, obj, group=self._group)
         return out
@@ -720,6 +732,7 @@ class P2PCommunicator(_CudaOps):
                 g = max(g, int(mg.value))
             else:
                 want_mc = False
+                self._mc_error = "cuMulticastGetGranularity: " + lib.dl_last_error().decode()
         self.heap_bytes = _round_up(self.heap_bytes, g)
         job = self._all_gather_obj(uuid.uuid4().hex[:12])[0]
         handle, fd = C.c_uint64(0), C.c_int(-1)
@@ -728,7 +741,8 @@ class P2PCommunicator(_CudaOps):
         sock = C.c_int(-1)
         name = lambda r: f"dlb200-{job}-{r}".encode()  # noqa: E731
         _lib.check(lib.dl_uds_listen(name(self.rank), C.byref(sock)))
-        self._dist.barrier(group=self._group)  # every listener is up
+        if self.world > 1:
+            self._dist.barrier(group=self._group)  # every listener is up
 
         received, errors = {}, []
         expect = (self.world - 1) + (1 if (want_mc and self.rank != 0) else 0)
@@ -792,6 +806,8 @@ class P2PCommunicator(_CudaOps):
                     mc_ok, mch = False, None
             if mc_ok:
                 mc_ok = lib.dl_mc_add_device(mch, dev) == 0
+                if not mc_ok:
+                    self._mc_error = lib.dl_last_error().decode()
             mc_ok = all(self._all_gather_obj(bool(mc_ok)))
             if mc_ok:
                 mc_ok = lib.dl_mc_bind(mch, self._mem_handle, self.heap_bytes) == 0
