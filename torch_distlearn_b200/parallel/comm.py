@@ -153,7 +153,9 @@ class _VariantTable:
                 # a damaged table must not pass silently for a measured one: say so once, keep the defaults
                 import warnings
                 warnings.warn(f"distlearn_b200: ignoring variant table {path}: {e!r}; using built-in defaults")
-        self.light_permille = int(os.environ.get("DL_B200_LIGHT_PERMILLE", "1000"))
+        # per-bucket (light) launches: all of it through the switch where that wins beside the convolutions (measured at 8
+        # GPUs); at 2 GPUs the plain P2P form is the measured default.  DL_B200_LIGHT_PERMILLE overrides at any world.
+        self.light_permille = int(os.environ.get("DL_B200_LIGHT_PERMILLE", "0" if world == 2 else "1000"))
         self.forced = os.environ.get("DL_B200_VARIANT")
         if os.environ.get("DL_B200_NVLS_PERMILLE"):
             self.hybrid_permille = {op: int(os.environ["DL_B200_NVLS_PERMILLE"]) for op in self.OPS}
@@ -501,7 +503,7 @@ class _CudaOps(Communicator):
             # Beside the convolutions the switch path is the one that pays: a multimem load is one instruction per 16 bytes
             # of EIGHT ranks' data, where the P2P form spends eight loads and eight stores of the SMs it shares (8 GPUs,
             # per-layer buckets: 898k samples/s all-switch, 830k at 750/1000, 821k all-P2P, 879k without buckets).
-            self._c.nvls_permille = self._variants.light_permille if (self.has_multicast and self.world != 2) else 0
+            self._c.nvls_permille = self._variants.light_permille if self.has_multicast else 0
         with torch.cuda.device(self.device), _Range(f"distlearn.fused_sgd[{VARIANT_TEXT[v]}]"):
             _lib.check(self._lib.dl_fused_sgd(C.byref(self._c), grads.offset, params.offset,
                                               momentum_buf.offset if momentum_buf else 0, n, lr, momentum, weight_decay,
