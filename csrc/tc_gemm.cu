@@ -61,6 +61,8 @@ struct GemmArgs {
   int cH, cW;             // image height / width
   int cA;                 // channels of the 4-D tensor on the A side (mode 1: Cin, mode 2: Cout)
   int cIn;                // Cin (modes 2 and 3)
+  int b_split;            // stream-K kernel only: the B operand arrives already split (map_b = hi, map_b2 = lo, made once
+                          // per step by dl_split_tf32): the converter warps leave B alone
 };
 
 // ---- PTX wrappers ------------------------------------------------------------------------------
@@ -898,7 +900,7 @@ extern "C" int dl_tc_gemm_ex(const float* A, const float* B, float* C, const flo
   g.terms = terms;
   g.a_mn = a_mn ? 1 : 0;
   g.b_mn = b_mn ? 1 : 0;
-  g.mode = 0; g.cH = g.cW = g.cA = g.cIn = 0;
+  g.mode = 0; g.cH = g.cW = g.cA = g.cIn = 0; g.b_split = 0;
   g.vec_out = (reinterpret_cast<uintptr_t>(C) % 16 == 0 && ldc % 4 == 0 &&
                (bias == nullptr || reinterpret_cast<uintptr_t>(bias) % 16 == 0)) ? 1 : 0;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
@@ -917,7 +919,7 @@ extern "C" int dl_tc_gemm_ex(const float* A, const float* B, float* C, const flo
   if (rc != DL_OK) return rc;
   rc = b_mn ? make_map(&mb, B, K, N, ldb, BK, 1) : make_map(&mb, B, N, K, ldb, bn, 0);
   if (rc != DL_OK) return rc;
-  if (use_ts() && use_streamk()) return bn == 64 ? launch_sk<64>(ma, mb, g, accumulate, st) : launch_sk<128>(ma, mb, g, accumulate, st);
+  if (use_ts() && use_streamk()) return bn == 64 ? launch_sk<64>(ma, mb, mb, g, accumulate, st) : launch_sk<128>(ma, mb, mb, g, accumulate, st);
   if (splits > 1 && !accumulate) {
     // split-K partial sums are added with atomics: start from zero (row by row: C may be a strided view)
     if (ldc == N) {
@@ -934,13 +936,57 @@ extern "C" int dl_tc_gemm(const float* A, const float* B, float* C, const float*
   return dl_tc_gemm_ex(A, B, C, bias, M, N, K, lda, ldb, ldc, 0, 0, split_k, accumulate, terms, stream);
 }
 
+// hi = w rounded to TF32 (the converter warps' rounding), lo = w - hi: the two B operands of the 3xTF32 product, made
+// once per step and layer instead of once per K block and CTA.  n % 4 == 0, 16-byte aligned pointers.
+namespace {
+__global__ void split_tf32_kernel(const float4* __restrict__ w, float4* __restrict__ hi, float4* __restrict__ lo, long long n4) {
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n4; i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const float4 v = w[i];
+    const float4 h = make_float4(tf32_round(v.x), tf32_round(v.y), tf32_round(v.z), tf32_round(v.w));
+    hi[i] = h;
+    lo[i] = make_float4(v.x - h.x, v.y - h.y, v.z - h.z, v.w - h.w);
+  }
+}
+}  // namespace
+
+extern "C" int dl_split_tf32(const float* w, float* hi, float* lo, long long n, void* stream) {
+  DL_REQUIRE(w && hi && lo && n > 0 && n % 4 == 0, "dl_split_tf32: bad arguments (n must be a positive multiple of 4)");
+  DL_REQUIRE((reinterpret_cast<uintptr_t>(w) | reinterpret_cast<uintptr_t>(hi) | reinterpret_cast<uintptr_t>(lo)) % 16 == 0,
+             "dl_split_tf32: pointers must be 16-byte aligned");
+  const long long n4 = n / 4;
+  long long blocks = (n4 + 255) / 256;
+  if (blocks > 1184) blocks = 1184;
+  split_tf32_kernel<<<static_cast<unsigned>(blocks), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      reinterpret_cast<const float4*>(w), reinterpret_cast<float4*>(hi), reinterpret_cast<float4*>(lo), n4);
+  dl_note_launch();
+  DL_CUDA(cudaGetLastError());
+  return DL_OK;
+}
+
 // Implicit-GEMM 5x5 / stride 1 / pad 2 convolution pieces on NHWC tensors (see GemmArgs::mode).
 //   mode 1: act = x  [B,H,W,Cin],  w = W[Cout, 25*Cin], out = y  [B*H*W, Cout] (+ bias)
 //   mode 2: act = dy [B,H,W,Cout], w = W,               out = dx [B*H*W, Cin]
 //   mode 3: act = x  [B,H,W,Cin],  w = dy [B*H*W, Cout] (the other operand), out = dW [Cout, 25*Cin]
+//
+// dl_tc_conv5x5_ws: the same with the weights ALSO given as their TF32 split (w_hi = w rounded to TF32, w_lo = w - w_hi,
+// both [Cout, 25*Cin], made by dl_split_tf32).  Modes 1 and 2 of the 3xTF32 stream-K kernel then load both halves by
+// TMA and the converter warps only handle the activations: per K block 48 KB less shared-memory traffic (B read, B hi
+// and lo written back) for 16 KB more TMA — the kernel is bound by the shared-memory port (profiles/ncu_gemm_r2.md).
+// Same products, same order, same bits.  Anything else (mode 3, terms 1, the one-tile-per-CTA kernels) ignores the split.
+extern "C" int dl_tc_conv5x5_ws(int mode, const float* act, const float* w, const float* w_hi, const float* w_lo, float* out,
+                                const float* bias, int B, int H, int W, int Cin, int Cout, int split_k, int accumulate, int terms,
+                                void* stream);
+
 extern "C" int dl_tc_conv5x5(int mode, const float* act, const float* w, float* out, const float* bias, int B, int H, int W,
                              int Cin, int Cout, int split_k, int accumulate, int terms, void* stream) {
+  return dl_tc_conv5x5_ws(mode, act, w, nullptr, nullptr, out, bias, B, H, W, Cin, Cout, split_k, accumulate, terms, stream);
+}
+
+extern "C" int dl_tc_conv5x5_ws(int mode, const float* act, const float* w, const float* w_hi, const float* w_lo, float* out,
+                                const float* bias, int B, int H, int W, int Cin, int Cout, int split_k, int accumulate, int terms,
+                                void* stream) {
   DL_REQUIRE(mode >= 1 && mode <= 3, "dl_tc_conv5x5: mode must be 1 (forward), 2 (dgrad) or 3 (wgrad)");
+  DL_REQUIRE((w_hi == nullptr) == (w_lo == nullptr), "dl_tc_conv5x5_ws: give both halves of the split or neither");
   DL_REQUIRE(act && w && out && B > 0 && H > 0 && W > 0, "dl_tc_conv5x5: bad arguments");
   DL_REQUIRE(Cin % BK == 0 && Cout % BK == 0, "dl_tc_conv5x5: Cin (%d) and Cout (%d) must be multiples of %d", Cin, Cout, BK);
   DL_REQUIRE(terms == 1 || terms == 3, "dl_tc_conv5x5: terms must be 1 or 3");
@@ -954,7 +1000,8 @@ extern "C" int dl_tc_conv5x5(int mode, const float* act, const float* w, float* 
   g.C = out; g.bias = mode == 1 ? bias : nullptr; g.terms = terms;
   g.mode = mode; g.cH = H; g.cW = W; g.cIn = Cin;
   g.a_mn = mode == 3; g.b_mn = mode != 1;
-  CUtensorMap ma, mb;
+  g.b_split = (w_hi != nullptr && mode != 3 && terms == 3 && use_ts() && use_streamk()) ? 1 : 0;
+  CUtensorMap ma, mb, mb2;
   int rc;
   if (mode == 1) {
     g.M = static_cast<int>(pixels); g.N = Cout; g.K = kc; g.cA = Cin;
@@ -971,10 +1018,16 @@ extern "C" int dl_tc_conv5x5(int mode, const float* act, const float* w, float* 
     if (rc != DL_OK) return rc;
   }
   const int bn = g.N <= 64 ? 64 : 128;
-  if (mode == 1) rc = make_map(&mb, w, Cout, kc, kc, bn, 0);             // W K-major
-  else if (mode == 2) rc = make_map(&mb, w, Cout, kc, kc, BK, 1);        // W MN-major: rows = cout (K), cols = (tap, cin)
+  const float* wb = g.b_split ? w_hi : w;
+  if (mode == 1) rc = make_map(&mb, wb, Cout, kc, kc, bn, 0);            // W K-major
+  else if (mode == 2) rc = make_map(&mb, wb, Cout, kc, kc, BK, 1);       // W MN-major: rows = cout (K), cols = (tap, cin)
   else rc = make_map_nhwc(&mb, act, B, H, W, Cin, BK, true);             // X as MN-major B, 32-pixel boxes
   if (rc != DL_OK) return rc;
+  mb2 = mb;
+  if (g.b_split) {
+    rc = mode == 1 ? make_map(&mb2, w_lo, Cout, kc, kc, bn, 0) : make_map(&mb2, w_lo, Cout, kc, kc, BK, 1);
+    if (rc != DL_OK) return rc;
+  }
   g.ldc = g.N;
   const int total_kb = (g.K + BK - 1) / BK;
   if (split_k < 1) split_k = 1;
@@ -985,7 +1038,7 @@ extern "C" int dl_tc_conv5x5(int mode, const float* act, const float* w, float* 
   g.vec_out = (reinterpret_cast<uintptr_t>(out) % 16 == 0 && g.ldc % 4 == 0 &&
                (g.bias == nullptr || reinterpret_cast<uintptr_t>(g.bias) % 16 == 0)) ? 1 : 0;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  if (use_ts() && use_streamk()) return bn == 64 ? launch_sk<64>(ma, mb, g, accumulate, st) : launch_sk<128>(ma, mb, g, accumulate, st);
+  if (use_ts() && use_streamk()) return bn == 64 ? launch_sk<64>(ma, mb, mb2, g, accumulate, st) : launch_sk<128>(ma, mb, mb2, g, accumulate, st);
   if (splits > 1 && !accumulate) DL_CUDA(cudaMemsetAsync(out, 0, static_cast<size_t>(g.M) * g.N * 4, st));
   return bn == 64 ? launch<64>(ma, mb, g, splits, st) : launch<128>(ma, mb, g, splits, st);
 }

@@ -40,7 +40,8 @@ __host__ __device__ __forceinline__ SkSegment sk_segment(const SkArgs& k, long l
 
 template <int BN>
 __global__ void __launch_bounds__(TS_THREADS, 1)
-tc_gemm_sk_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, GemmArgs g, SkArgs k) {
+tc_gemm_sk_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+                  const __grid_constant__ CUtensorMap map_b2, GemmArgs g, SkArgs k) {
   extern __shared__ __align__(1024) unsigned char smem_raw[];
   SmemTS<BN>& s = *reinterpret_cast<SmemTS<BN>*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -78,7 +79,7 @@ tc_gemm_sk_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
           const int m0 = sg.m0, n0 = sg.n0;
           for (int i = 0; i < sg.nkb; ++i) {
             mbar_wait(&s.empty[st], (it & 1) ^ 1);
-            mbar_expect_tx(&s.full[st], (BM + BN) * BK * 4);
+            mbar_expect_tx(&s.full[st], (BM + (g.b_split ? 2 * BN : BN)) * BK * 4);
             const int kb = sg.kb0 + i;
             const int k0 = kb * BK;
             if (g.mode == 1 || g.mode == 2) {
@@ -91,9 +92,13 @@ tc_gemm_sk_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
               tma_load_4d(&s.a[st][0], &map_a, &s.full[st], cb * BK, dw, h0 + dh, b0);
               if (g.mode == 1) {
                 tma_load_2d(&s.b[st][0][0], &map_b, &s.full[st], k0, n0);
+                if (g.b_split) tma_load_2d(&s.b[st][1][0], &map_b2, &s.full[st], k0, n0);
               } else {
                 for (int bx = 0; bx < BN / 32; ++bx)
                   tma_load_2d(&s.b[st][0][bx * 32 * BK], &map_b, &s.full[st], tap * g.cIn + n0 + 32 * bx, cb * BK);
+                if (g.b_split)
+                  for (int bx = 0; bx < BN / 32; ++bx)
+                    tma_load_2d(&s.b[st][1][bx * 32 * BK], &map_b2, &s.full[st], tap * g.cIn + n0 + 32 * bx, cb * BK);
               }
             } else if (g.mode == 3) {
               for (int bx = 0; bx < BM / 32; ++bx) tma_load_2d(&s.a[st][bx * 32 * BK], &map_a, &s.full[st], m0 + 32 * bx, k0);
@@ -172,6 +177,7 @@ tc_gemm_sk_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
       const uint32_t a_base = smem_u32(&s.a[0][0]), b_base = smem_u32(&s.b[0][0][0]);
       constexpr uint32_t A_TILE = BM * BK * 4, B_TILE = BN * BK * 4;
       const bool three = g.terms == 3;
+      const bool conv_b = g.b_split == 0;                    // B arrives split (hi and lo by TMA): nothing to do for it here
       const int quarter = warp & 3;
       const int half = (warp - 2) >> 2;
       const int row = quarter * 32 + lane;
@@ -188,8 +194,10 @@ tc_gemm_sk_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
           float4 av[4];
 #pragma unroll
           for (int c = 0; c < 4; ++c) av[c] = lds128(a_tile + row * 128 + (((half * 4 + c) ^ (row & 7)) << 4));
+          if (conv_b) {
 #pragma unroll
-          for (int j = 0; j < NB; ++j) bv[j] = lds128(b_hi + j * 4096);
+            for (int j = 0; j < NB; ++j) bv[j] = lds128(b_hi + j * 4096);
+          }
 #pragma unroll
           for (int c = 0; c < 4; ++c) {
             const float e[4] = {av[c].x, av[c].y, av[c].z, av[c].w};
@@ -205,8 +213,10 @@ tc_gemm_sk_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
           float e[16];
 #pragma unroll
           for (int kk = 0; kk < 16; ++kk) e[kk] = lds32(colp + kk * 128);
+          if (conv_b) {
 #pragma unroll
-          for (int j = 0; j < NB; ++j) bv[j] = lds128(b_hi + j * 4096);
+            for (int j = 0; j < NB; ++j) bv[j] = lds128(b_hi + j * 4096);
+          }
 #pragma unroll
           for (int kk = 0; kk < 16; ++kk) {
             const float h = tf32_round(e[kk]);
@@ -217,15 +227,17 @@ tc_gemm_sk_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
         const uint32_t ta = tmem + (static_cast<uint32_t>(quarter * 32) << 16) + static_cast<uint32_t>(2 * BN + st * 64 + half * 16);
         tmem_st16(ta, hi);
         if (three) tmem_st16(ta + 32, lo);
+        if (conv_b) {
 #pragma unroll
-        for (int j = 0; j < NB; ++j) {
-          const float4 v = bv[j];
-          const float4 h = make_float4(tf32_round(v.x), tf32_round(v.y), tf32_round(v.z), tf32_round(v.w));
-          sts128(b_hi + j * 4096, h);
-          if (three) sts128(b_lo + j * 4096, make_float4(v.x - h.x, v.y - h.y, v.z - h.z, v.w - h.w));
+          for (int j = 0; j < NB; ++j) {
+            const float4 v = bv[j];
+            const float4 h = make_float4(tf32_round(v.x), tf32_round(v.y), tf32_round(v.z), tf32_round(v.w));
+            sts128(b_hi + j * 4096, h);
+            if (three) sts128(b_lo + j * 4096, make_float4(v.x - h.x, v.y - h.y, v.z - h.z, v.w - h.w));
+          }
         }
         asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        if (conv_b) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // (no generic-proxy writes to shared memory otherwise)
         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
         mbar_arrive(&s.conv[st]);
         if (++st == TS_STAGES) { st = 0; ++it; }
@@ -336,7 +348,7 @@ SkArgs sk_plan(int M, int N, int K, int bn, int sms, long long* grid) {
 
 // `accumulate`: C already holds values to add to (every segment uses red.add, nothing is zeroed)
 template <int BN>
-int launch_sk(const CUtensorMap& ma, const CUtensorMap& mb, GemmArgs g, int accumulate, cudaStream_t st) {
+int launch_sk(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mb2, GemmArgs g, int accumulate, cudaStream_t st) {
   static bool configured[64] = {false};
   static int sm_count[64] = {0};
   int dev = 0;
@@ -361,7 +373,7 @@ int launch_sk(const CUtensorMap& ma, const CUtensorMap& mb, GemmArgs g, int accu
       DL_CUDA(cudaMemset2DAsync(g.C, static_cast<size_t>(g.ldc) * 4, 0, static_cast<size_t>(g.N) * 4, g.M, st));
     }
   }
-  tc_gemm_sk_kernel<BN><<<static_cast<unsigned>(grid), TS_THREADS, smem, st>>>(ma, mb, g, k);
+  tc_gemm_sk_kernel<BN><<<static_cast<unsigned>(grid), TS_THREADS, smem, st>>>(ma, mb, mb2, g, k);
   dl_note_launch();
   DL_CUDA(cudaGetLastError());
   return DL_OK;

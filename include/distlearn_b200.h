@@ -251,6 +251,15 @@ int dl_tc_gemm_ex(const float* A, const float* B, float* C, const float* bias, i
  *   mode 3 wgrad  : act = x [B,H,W,Cin],  w = dy [B*H*W, Cout],                        out = dW [Cout, 25*Cin] */
 int dl_tc_conv5x5(int mode, const float* act, const float* w, float* out, const float* bias, int B, int H, int W,
                   int Cin, int Cout, int split_k, int accumulate, int terms, void* stream);
+/* The same with the weights also given as their TF32 split (w_hi = w rounded to TF32, w_lo = w - w_hi, both
+ * [Cout, 25*Cin], from dl_split_tf32): forward and dgrad of the 3xTF32 stream-K kernel then load both halves by TMA and
+ * its converter warps only handle the activations (less shared-memory traffic; same bits).  w_hi = w_lo = NULL, mode 3 and
+ * terms 1 behave exactly like dl_tc_conv5x5. */
+int dl_tc_conv5x5_ws(int mode, const float* act, const float* w, const float* w_hi, const float* w_lo, float* out,
+                     const float* bias, int B, int H, int W, int Cin, int Cout, int split_k, int accumulate, int terms,
+                     void* stream);
+/* hi[i] = w[i] rounded to TF32, lo[i] = w[i] - hi[i]; n a multiple of 4, 16-byte aligned pointers. */
+int dl_split_tf32(const float* w, float* hi, float* lo, long long n, void* stream);
 
 /* Stream-K form of the tensor-core GEMM — one persistent CTA per SM takes a contiguous range of (tile, K-block) units,
  * so 256 tiles on 148 SMs cost 86.5 K-block times instead of 100 (csrc/tc_gemm_streamk.inl).  on = 1 / 0 switches it

@@ -18,6 +18,7 @@ wgrad).  The explicit im2col / col2im path remains for Cin = 3.
 from __future__ import annotations
 
 import math
+import os
 from typing import Optional
 
 import torch
@@ -83,12 +84,55 @@ def _implicit_ok(B: int, H: int, W: int, cin: int, cout: int) -> bool:
 
 
 def _tc_conv(mode: int, act: torch.Tensor, w: torch.Tensor, out: torch.Tensor, bias, B, H, W, cin, cout, split_k, terms,
-             accumulate: bool = False) -> torch.Tensor:
+             accumulate: bool = False, w_split: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """``w_split``: [2, Cout, 25*Cin] = (hi, lo) of ``w`` from :func:`split_weights` — modes 1 and 2 then take the weights
+    already split (csrc/tc_gemm.cu: dl_tc_conv5x5_ws)."""
     with torch.cuda.device(act.device):
-        _lib.check(_lib.cuda().dl_tc_conv5x5(mode, act.data_ptr(), w.data_ptr(), out.data_ptr(),
-                                             bias.data_ptr() if bias is not None else None, B, H, W, cin, cout, int(split_k),
-                                             int(accumulate), int(terms), _stream(act)))
+        _lib.check(_lib.cuda().dl_tc_conv5x5_ws(mode, act.data_ptr(), w.data_ptr(),
+                                                w_split[0].data_ptr() if w_split is not None else None,
+                                                w_split[1].data_ptr() if w_split is not None else None, out.data_ptr(),
+                                                bias.data_ptr() if bias is not None else None, B, H, W, cin, cout, int(split_k),
+                                                int(accumulate), int(terms), _stream(act)))
     return out
+
+
+# Pre-split weights (hi = TF32(w), lo = w - hi), one persistent buffer per weight tensor: made once per forward pass and used
+# by the forward and the dgrad GEMM of that step, instead of being re-made by the converter warps of every CTA in every K
+# block.  DL_B200_TC_PRESPLIT=0 (or presplit(False)) switches it off.
+_PRESPLIT = os.environ.get("DL_B200_TC_PRESPLIT", "1") != "0"
+_SPLITS: dict = {}
+
+
+def presplit(on: Optional[bool] = None) -> bool:
+    """Query / set whether the convolutions hand their weights to the GEMM already split."""
+    global _PRESPLIT
+    before = _PRESPLIT
+    if on is not None:
+        _PRESPLIT = bool(on)
+    return before
+
+
+class _Split:
+    __slots__ = ("buf", "seq")
+
+    def __init__(self, w: torch.Tensor):
+        self.buf = torch.empty((2,) + tuple(w.shape), dtype=torch.float32, device=w.device)
+        self.seq = 0
+
+
+def split_weights(w: torch.Tensor) -> "_Split":
+    """(Re)compute the split of ``w`` into its persistent buffer on the current stream; returns the cache entry
+    (``.buf`` [2, ...], ``.seq`` counts the recomputations so a backward pass can tell whether the buffer still is its own)."""
+    key = (w.data_ptr(), tuple(w.shape), w.device.index)
+    e = _SPLITS.get(key)
+    if e is None:
+        if len(_SPLITS) >= 64:      # short-lived weight tensors (tests, sweeps): do not let their buffers pile up
+            _SPLITS.clear()         # (a pending backward pass keeps its own entry alive through ctx.split)
+        e = _SPLITS[key] = _Split(w)
+    with torch.cuda.device(w.device):
+        _lib.check(_lib.cuda().dl_split_tf32(w.data_ptr(), e.buf[0].data_ptr(), e.buf[1].data_ptr(), w.numel(), _stream(w)))
+    e.seq += 1
+    return e
 
 
 class _Conv5x5Implicit(torch.autograd.Function):
@@ -102,8 +146,11 @@ class _Conv5x5Implicit(torch.autograd.Function):
         M = B * H * W
         bn = 64 if cout <= 64 else 128
         y = torch.empty(M, cout, dtype=torch.float32, device=x.device)
-        _tc_conv(1, x, weight, y, bias, B, H, W, C, cout, _splits((M + 127) // 128, (cout + bn - 1) // bn, TAPS * C), terms)
+        split = split_weights(weight.detach()) if (_PRESPLIT and terms == 3 and weight.is_contiguous()) else None
+        _tc_conv(1, x, weight, y, bias, B, H, W, C, cout, _splits((M + 127) // 128, (cout + bn - 1) // bn, TAPS * C), terms,
+                 w_split=split.buf if split is not None else None)
         ctx.save_for_backward(x, weight)
+        ctx.split = (split, split.seq) if split is not None else None
         ctx.meta = (terms, bias is not None)
         ctx.params = (weight, bias)
         return y.view(B, H, W, cout)
@@ -135,7 +182,14 @@ class _Conv5x5Implicit(torch.autograd.Function):
         if ctx.needs_input_grad[0]:
             bn = 64 if C <= 64 else 128
             dx = torch.empty(B, H, W, C, dtype=torch.float32, device=x.device)
-            _tc_conv(2, dy, weight, dx, None, B, H, W, C, cout, _splits((M + 127) // 128, (C + bn - 1) // bn, TAPS * cout), terms)
+            w_split = None
+            if ctx.split is not None:
+                split, seq = ctx.split
+                if split.seq != seq:          # another forward pass has used the buffer since: make it ours again
+                    split = split_weights(weight.detach())
+                w_split = split.buf
+            _tc_conv(2, dy, weight, dx, None, B, H, W, C, cout, _splits((M + 127) // 128, (C + bn - 1) // bn, TAPS * cout), terms,
+                     w_split=w_split)
         # only now, with the dgrad GEMM (which reads the weights) enqueued, may a listener start updating this layer
         for p, g in zip(ctx.params, (dw, db)):
             if p is not None and g is None:
