@@ -140,7 +140,7 @@ def cuda():
     _sig(lib, "dl_tc_gemm_ex", i32, [vp, vp, vp, vp, i32, i32, i32, C.c_longlong, C.c_longlong, C.c_longlong, i32, i32, i32, i32, i32, vp])
     _sig(lib, "dl_tc_conv5x5", i32, [i32, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, vp])
     _sig(lib, "dl_tc_conv5x5_ws", i32, [i32, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, vp])
-    _sig(lib, "dl_split_tf32", i32, [vp, vp, vp, i64, vp])
+    _sig(lib, "dl_split_tf32", i32, [vp, vp, vp, C.c_longlong, vp])
     _sig(lib, "dl_tc_gemm_streamk", i32, [i32])
     _sig(lib, "dl_tc_streamk_plan", i32, [i32, i32, i32, i32, i32, P(i32), P(i32), i32])
     _sig(lib, "dl_bn_work_bytes", sz, [i32])
