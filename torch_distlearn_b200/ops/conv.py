@@ -98,8 +98,11 @@ def _tc_conv(mode: int, act: torch.Tensor, w: torch.Tensor, out: torch.Tensor, b
 
 # Pre-split weights (hi = TF32(w), lo = w - hi), one persistent buffer per weight tensor: made once per forward pass and used
 # by the forward and the dgrad GEMM of that step, instead of being re-made by the converter warps of every CTA in every K
-# block.  DL_B200_TC_PRESPLIT=0 (or presplit(False)) switches it off.
-_PRESPLIT = os.environ.get("DL_B200_TC_PRESPLIT", "1") != "0"
+# block.  OFF by default: measured on a B200 it is correct (tests/test_conv_presplit_gpu.py) and changes nothing — the
+# forward GEMMs take 71.0 / 67.1 us with it against 71.2 / 67.3 without, the step 1.141 ms against 1.121 with the three
+# split launches added (profiles/r2/r2k_*) — which is what says the GEMM is not bound by its converter warps
+# (profiles/ncu_gemm_r2.md).  DL_B200_TC_PRESPLIT=1 or presplit(True) switches it on.
+_PRESPLIT = os.environ.get("DL_B200_TC_PRESPLIT", "0") == "1"
 _SPLITS: dict = {}
 
 
