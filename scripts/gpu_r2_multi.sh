@@ -13,14 +13,15 @@ timeout 120 $TR --master-port 29561 bench/peak.py --mb 256 --out gpurun_out/nvli
 mkdir -p profiles && cp gpurun_out/nvlink_peak_$N.json profiles/nvlink_peak.json 2>/dev/null
 fi
 MAXMB=1024; [ "$MODE" = "lite" ] && MAXMB=64
-timeout 500 $TR --master-port 29541 bench/sweep.py --max-mb $MAXMB --permille 0,600,750,1000 --write-table --out gpurun_out/${P}_sweep_$N.json > gpurun_out/${P}_sweep_$N.log 2>&1; echo "sweep rc=$? ($(( $(date +%s) - t0 ))s)"
+PM=0,600,750,1000; [ "$MODE" = "final" ] && PM=750,1000
+timeout 500 $TR --master-port 29541 bench/sweep.py --max-mb $MAXMB --permille $PM --write-table --out gpurun_out/${P}_sweep_$N.json > gpurun_out/${P}_sweep_$N.log 2>&1; echo "sweep rc=$? ($(( $(date +%s) - t0 ))s)"
 grep "variant table" gpurun_out/${P}_sweep_$N.log | cut -c1-400
 timeout 300 $TR --master-port 29542 bench/sweep.py --max-mb 64 --permille 0,750,1000 --graph --write-table --out gpurun_out/${P}_sweep_${N}_graph.json > gpurun_out/${P}_sweep_${N}_graph.log 2>&1; echo "sweep graph rc=$? ($(( $(date +%s) - t0 ))s)"
 grep "variant table" gpurun_out/${P}_sweep_${N}_graph.log | cut -c1-400
 # install the freshly measured table for the benches below (world N entry)
 python scripts/merge_variant_table.py gpurun_out/variant_table_${N}_graph.json $N; echo "table merge rc=$?"
 b() { name=$1; shift; timeout 200 $TR --master-port 29551 bench.py --gpus $N --steps 100 --warmup 10 "$@" > gpurun_out/${P}_bench${N}_$name.log 2>&1; echo "bench $name rc=$? $(tail -n 1 gpurun_out/${P}_bench${N}_$name.log | cut -c1-160)"; }
-b b0 --baselines 0 --bucket-mb 0
+[ "$MODE" != "final" ] && b b0 --baselines 0 --bucket-mb 0
 [ "$MODE" != "final" ] && b exe05 --baselines 0 --bucket-mb 0.5 --flat-order execution
 if [ "$MODE" = "full" ]; then
 b exe05_b74 --baselines 0 --bucket-mb 0.5 --flat-order execution --bucket-blocks 74
@@ -28,7 +29,7 @@ b exe1 --baselines 0 --bucket-mb 1 --flat-order execution
 fi
 b default
 b gb32 --global-batch 32
-b ea --algo ea
+if [ "$MODE" = "final" ]; then b ea --algo ea --baselines 0; else b ea --algo ea; fi
 echo "benches done ($(( $(date +%s) - t0 ))s)"
 IMPLS="ours ours_eager hostloop"; [ "$MODE" = "lite" ] && IMPLS="ours hostloop"; [ "$MODE" = "final" ] && IMPLS="ours"
 for impl in $IMPLS; do
