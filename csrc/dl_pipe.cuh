@@ -25,8 +25,13 @@
 #include "dl_common.cuh"
 
 #define DL_PIPE_THREADS 256
-#define DL_PIPE_MC_U 8  // multimem.ld_reduce vectors per thread per stage (2 stages in flight): the switch round trip is long —
-                        // with 4 the 8-GPU all-switch pass moved 528 GB/s per direction where the two phases alone do 715-725
+// multimem.ld_reduce vectors per thread per stage (2 stages in flight).  Measured on 8 GPUs, graph-timed, all-switch pass
+// (profiles/r2/r2_sweep_8_graph.json with 4, r2z_sweep_8_graph.json with 8): 1 MiB 15.3 -> 13.9 us, 4 MiB 22.7 -> 21.3,
+// 16 MiB 60.9 -> 59.7, but 64 MiB 179.4 -> 198.8: short passes want more loads in flight, long ones saturate the switch
+// and then queue.  So: 8 while a rank's slice is below DL_PIPE_MC_BIG float4 (4 MiB), 4 from there on.
+#define DL_PIPE_MC_U 8
+#define DL_PIPE_MC_U_BIG 4
+#define DL_PIPE_MC_BIG (1ull << 18)
 
 struct DlPipeRange {
   unsigned long long r0, r1;  // slice-relative range of this block in float4 units (both even)
@@ -137,10 +142,9 @@ __device__ __forceinline__ void dl_pipe_p2p(const dl_comm_t& c, int world, uint3
 
 // ---- switch path: items of DL_PIPE_MC_U x 16 bytes ------------------------------------------------------
 // Epi::mc(float4 sum_over_all_ranks, idx) -> float4 to distribute.
-template <typename Epi>
+template <int U, typename Epi>
 __device__ __forceinline__ void dl_pipe_mc(const dl_comm_t& c, uint64_t src_off, uint64_t dst_off, uint64_t dst2_off,
                                            unsigned long long begin4, unsigned long long end4, Epi& epi) {
-  constexpr int U = DL_PIPE_MC_U;
   const float4* msrc = dl_mc_at<float4>(c, src_off);
   float4* mdst = dl_mc_at<float4>(c, dst_off);
   float4* mdst2 = dst2_off ? dl_mc_at<float4>(c, dst2_off) : nullptr;
@@ -184,7 +188,8 @@ __device__ __forceinline__ void dl_pipe_pass(const dl_comm_t& c, int rank, int w
   if (b4 > s.end) b4 = s.end;
   if (e4 > s.end) e4 = s.end;
   if (g.nvls) {
-    dl_pipe_mc(c, src_off, dst_off, dst2_off, b4, e4, epi);
+    if (s.slice4 >= DL_PIPE_MC_BIG) dl_pipe_mc<DL_PIPE_MC_U_BIG>(c, src_off, dst_off, dst2_off, b4, e4, epi);
+    else dl_pipe_mc<DL_PIPE_MC_U>(c, src_off, dst_off, dst2_off, b4, e4, epi);
   } else {
     dl_pipe_p2p<W>(c, world, lmask, src_off, dst_off, dst2_off, b4, e4, epi);
   }
