@@ -152,9 +152,11 @@ __global__ void __launch_bounds__(DL_THREADS) ll_kernel(dl_comm_t c, LlArgs a) {
       own[u] = in[idx];
       for (int j = 0; j < world; ++j) {
         if (j == rank) continue;
-        uint4* slot = ll_slot(c, j, a.channel, parity, rank) + 1 + 2 * idx;
+        // the two packets of vector idx sit nvec apart, not side by side: a warp's store then covers 512 contiguous bytes
+        // (four full lines on the link) instead of 16 bytes out of every 32
+        uint4* slot = ll_slot(c, j, a.channel, parity, rank) + 1 + idx;
         dl_ll_store(slot, own[u].x, own[u].y, flag);
-        dl_ll_store(slot + 1, own[u].z, own[u].w, flag);
+        dl_ll_store(slot + a.nvec, own[u].z, own[u].w, flag);
       }
     }
   }
@@ -204,9 +206,9 @@ __global__ void __launch_bounds__(DL_THREADS) ll_kernel(dl_comm_t c, LlArgs a) {
 #pragma unroll
       for (int j = 0; j < DL_MAX_RANKS; ++j) {
         if ((pending >> j) & 1u) {
-          const uint4* slot = ll_slot(c, rank, a.channel, parity, j) + 1 + 2 * idx;
+          const uint4* slot = ll_slot(c, rank, a.channel, parity, j) + 1 + idx;
           p0[j] = dl_ll_load(slot);
-          p1[j] = dl_ll_load(slot + 1);
+          p1[j] = dl_ll_load(slot + a.nvec);
         }
       }
 #pragma unroll
