@@ -11,7 +11,7 @@ With ``--fused`` (default) those two become ONE launch of the fused sm_100a kern
 iterations the confusion matrix is summed over the nodes (:119-125), at the end of every epoch the
 parameters are re-synchronised (:129), which also absorbs uneven partition sizes.
 """
-from common import batches_this_epoch, forward_backward, min_over_nodes, setup, Throughput
+from common import batches_this_epoch, forward_backward, min_over_nodes, setup, Throughput, MnistKernelStep
 
 import torch
 
@@ -26,6 +26,7 @@ from torch_distlearn_b200.utils.data import MNIST_CLASSES
 def main(argv=None):
     p = base_parser("MNIST AllReduceSGD (examples/mnist.lua)", batch_size=1, learning_rate=0.01)
     p.add_argument("--reportEvery", type=int, default=1000)
+    p.add_argument("--eager", action="store_true", help="torch forward/backward instead of the one-launch kernel (GPU)")
     opt = p.parse_args(argv)
     comm, log = setup(opt)
     dev = comm.device
@@ -46,12 +47,19 @@ def main(argv=None):
     cm = ConfusionMatrix(MNIST_CLASSES, comm=comm)
     n_batches = batches_this_epoch(num_batches(), opt)
     common_batches = min_over_nodes(comm, n_batches)               # periodic reports need every node present
+    kstep = None
+    if MnistKernelStep.usable(model, dev, opt.batchSize) and not opt.eager:
+        kstep = MnistKernelStep(model, opt.batchSize)              # forward + backward in one launch (csrc/mnist_step.cu);
+                                                                   # it ADDS into .grad like autograd, the all-reduce follows
     for epoch in range(start_epoch, opt.numEpochs + 1):
         cm.zero()
         thr, loss_sum = Throughput(), 0.0
         for i in range(1, n_batches + 1):
             batch = get_batch()
-            out, loss = forward_backward(model, batch)
+            if kstep is not None and batch.input.shape[0] == opt.batchSize:
+                out, loss, _ = kstep(batch)
+            else:
+                out, loss = forward_backward(model, batch)
             if opt.fused:
                 sgd.step(lr=opt.learningRate, momentum=opt.momentum, weight_decay=opt.weightDecay, variant=opt.variant)
             else:
