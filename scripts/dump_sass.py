@@ -16,8 +16,15 @@ WANT = {
     "sgd_twoshot_kernelILi1ELb0ELb0E": "fused_sgd_w1",
     "tc_gemm_ts_kernelILi128E": "tc_gemm_ts_bn128", "tc_gemm_kernelILi128E": "tc_gemm_smemA_bn128",
     "bn_relu_pool_bwd_apply_kernel": "bn_relu_pool_bwd_apply", "bn_stats_kernel": "bn_stats",
+    # round 2
+    "9ll_kernelILi1ELi0ELb0E": "ll_fused_sgd", "9ll_kernelILi0ELi0ELb0E": "ll_allreduce_f32", "9ll_kernelILi3ELi0ELb0E": "ll_broadcast",
+    "sgd_pipe_kernelILi8ELb0E": "fused_sgd_hybrid_w8", "sgd_light_kernelILi8ELb0E": "fused_sgd_light_w8",
+    "allreduce_pipe_kernelILi8ELb0E": "allreduce_hybrid_w8", "fused_ea_pipe_kernelILi8ELb0E": "fused_ea_hybrid_w8",
+    "broadcast_wide_kernelILb1ELb0E": "broadcast_wide_mc", "broadcast_wide_kernelILb0ELb0E": "broadcast_wide_p2p",
+    "mnist_step_kernelILb1E": "mnist_step_form2", "tc_gemm_sk_kernelILi128E": "tc_gemm_streamk_bn128",
+    "litmus_kernelILb0E": "litmus",
 }
-KEYS = ("LD.E", "ST.E", "LDL", "STL", "LDGMC", "REDG", "RED.", "STG", "LDG", "ATOM", "MEMBAR", "CCTL", "ERRBAR", "UTC", "LDTM", "STTM", "UTMA", "UBLKCP", "SYNCS")
+KEYS = ("UCGABAR", "MAPA", "LD.E", "ST.E", "LDL", "STL", "LDGMC", "REDG", "RED.", "STG", "LDG", "ATOM", "MEMBAR", "CCTL", "ERRBAR", "UTC", "LDTM", "STTM", "UTMA", "UBLKCP", "SYNCS")
 
 
 def main():
