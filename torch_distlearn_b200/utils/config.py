@@ -31,7 +31,7 @@ def base_parser(description: str, batch_size: int = 32, learning_rate: float = 0
     p.add_argument("--testSamples", type=int, default=1024, help="size of the synthetic test set")
     p.add_argument("--momentum", type=float, default=0.0)
     p.add_argument("--weightDecay", type=float, default=0.0)
-    p.add_argument("--variant", choices=["auto", "oneshot", "twoshot", "nvls"], default="auto",
+    p.add_argument("--variant", choices=["auto", "ll", "oneshot", "twoshot", "nvls", "hybrid", "light"], default="auto",
                    help="collective algorithm (auto = measured variant table)")
     p.add_argument("--backend", choices=["auto", "p2p", "host", "dist"], default="auto",
                    help="p2p = CUDA symmetric heap over NVLink, host = CPU shared memory, "
